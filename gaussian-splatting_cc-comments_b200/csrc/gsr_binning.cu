@@ -1,0 +1,291 @@
+// gsr_binning.cu -- scan, stable radix sort, instance duplication and tile ranges for sm_100a.
+//
+// Replaces cub::DeviceScan::InclusiveSum (rasterizer_impl.cu:323-325), duplicateWithKeys
+// (:78-126), cub::DeviceRadixSort::SortPairs on (tile<<32 | depth_bits) (:357-374) and
+// identifyTileRanges (:133-159) of DGR/cuda_rasterizer/rasterizer_impl.cu.
+//
+// The reference sorts R = num_rendered 12-byte pairs on 32+bit key bits (6 passes at 1080p).
+// The same total order -- ascending (tile, depth bits), ties in ascending Gaussian index -- is
+// produced here in two cheaper steps, both stable LSD radix sorts on 32-bit keys:
+//   (1) sort the P Gaussians by depth bits (4 passes over P 8-byte pairs);
+//   (2) emit instances in that order and sort them by tile id only (2 passes over R 8-byte
+//       pairs for <= 65536 tiles).
+// Stability of (2) keeps depth order (and index order among equal depths) inside each tile.
+// All of it is HBM-bound integer work: coalesced key loads, warp-level match_any ranking in
+// shared memory, no tensor cores.
+#include "gsr_internal.cuh"
+#include "gsr_math.cuh"
+
+namespace gsr {
+
+// ------------------------------------------------------------------------------------------------
+// exclusive scan (three small kernels; sizes here are a few MB, launch-latency bound)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, int lane) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, v, d);
+        if (lane >= d) v += t;
+    }
+    return v;
+}
+
+// block-wide exclusive scan of one value per thread; returns exclusive prefix, *total = block sum
+template <int THREADS>
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* s_warp /* THREADS/32 + 1 */, uint32_t* total) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t inc = warp_incl_scan(v, lane);
+    if (lane == 31) s_warp[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        uint32_t x = (lane < THREADS / 32) ? s_warp[lane] : 0u;
+        const uint32_t xi = warp_incl_scan(x, lane);
+        if (lane < THREADS / 32) s_warp[lane] = xi - x;
+        if (lane == 31) s_warp[THREADS / 32] = xi;
+    }
+    __syncthreads();
+    const uint32_t r = s_warp[w] + inc - v;
+    *total = s_warp[THREADS / 32];
+    __syncthreads();
+    return r;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_block_sums_kernel(const uint32_t* __restrict__ in, size_t n, uint32_t* __restrict__ sums) {
+    __shared__ uint32_t s_warp[SCAN_THREADS / 32];
+    const size_t base = (size_t)blockIdx.x * SCAN_TILE;
+    uint32_t acc = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) {
+        const size_t i = base + (size_t)k * SCAN_THREADS + threadIdx.x;
+        if (i < n) acc += in[i];
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if ((threadIdx.x & 31) == 0) s_warp[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        uint32_t x = (threadIdx.x < SCAN_THREADS / 32) ? s_warp[threadIdx.x] : 0u;
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) x += __shfl_xor_sync(0xffffffffu, x, d);
+        if (threadIdx.x == 0) sums[blockIdx.x] = x;
+    }
+}
+
+// one block: exclusive scan of sums[0..nb) in place, sums[nb] = grand total
+__global__ void __launch_bounds__(1024) scan_sums_kernel(uint32_t* __restrict__ sums, size_t nb, uint32_t* __restrict__ total_out) {
+    __shared__ uint32_t s_warp[33];
+    uint32_t carry = 0;
+    for (size_t base = 0; base < nb; base += 1024) {
+        const size_t i = base + threadIdx.x;
+        const uint32_t v = (i < nb) ? sums[i] : 0u;
+        uint32_t tot;
+        const uint32_t ex = block_excl_scan<1024>(v, s_warp, &tot);
+        if (i < nb) sums[i] = carry + ex;
+        carry += tot;
+    }
+    if (threadIdx.x == 0) {
+        sums[nb] = carry;
+        if (total_out) *total_out = carry;
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, size_t n,
+                                                                  const uint32_t* __restrict__ sums) {
+    __shared__ uint32_t s_warp[SCAN_THREADS / 32 + 1];
+    const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS];
+    const bool full = ((size_t)blockIdx.x + 1) * SCAN_TILE <= n;
+    if (full) {
+        const uint4* p = reinterpret_cast<const uint4*>(in + base);
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS / 4; k++) {
+            const uint4 q = p[k];
+            v[4 * k] = q.x; v[4 * k + 1] = q.y; v[4 * k + 2] = q.z; v[4 * k + 3] = q.w;
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; k++) v[k] = (base + k < n) ? in[base + k] : 0u;
+    }
+    uint32_t tsum = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) tsum += v[k];
+    uint32_t tot;
+    uint32_t run = block_excl_scan<SCAN_THREADS>(tsum, s_warp, &tot) + sums[blockIdx.x];
+    uint32_t o[SCAN_ITEMS];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; k++) { o[k] = run; run += v[k]; }
+    if (full) {
+        uint4* p = reinterpret_cast<uint4*>(out + base);
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS / 4; k++) p[k] = make_uint4(o[4 * k], o[4 * k + 1], o[4 * k + 2], o[4 * k + 3]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; k++) if (base + k < n) out[base + k] = o[k];
+    }
+}
+
+void scan_exclusive_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t* tmp, uint32_t* total, cudaStream_t st) {
+    if (n == 0) {
+        if (total) cudaMemsetAsync(total, 0, sizeof(uint32_t), st);
+        return;
+    }
+    const size_t nb = scan_blocks(n);
+    scan_block_sums_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, n, tmp);
+    scan_sums_kernel<<<1, 1024, 0, st>>>(tmp, nb, total);
+    scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n, tmp);
+}
+
+// ------------------------------------------------------------------------------------------------
+// stable LSD radix sort pass on (u32 key, u32 value) pairs, <= 8 key bits per pass
+// ------------------------------------------------------------------------------------------------
+// Each block owns RS_TILE consecutive items; warp w owns the w-th 512-item slice and walks it in
+// 16 rounds of 32 consecutive items, so "earlier in the input" == (lower warp, lower round, lower
+// lane).  Within a round lanes with equal digits find each other with match.any; the lowest such
+// lane bumps the warp's private digit counter.  No atomics, fully deterministic.
+__device__ __forceinline__ void rs_rank_tile(const uint32_t* __restrict__ keys, size_t n, size_t tile_base, int shift, uint32_t mask,
+                                             uint32_t* s_hist /* [8][RS_BINS] */, uint32_t* key_out, uint32_t* rank_out) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    uint32_t* wh = s_hist + w * RS_BINS;
+    for (int i = lane; i < RS_BINS; i += 32) wh[i] = 0;
+    __syncwarp();
+    const uint32_t lt = (1u << lane) - 1u;
+    const size_t wbase = tile_base + (size_t)w * (32 * RS_ITEMS);
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; r++) {
+        const size_t i = wbase + (size_t)r * 32 + lane;
+        const bool valid = i < n;
+        const uint32_t key = valid ? keys[i] : 0u;
+        const uint32_t d = valid ? ((key >> shift) & mask) : 0xFFFFFFFFu;
+        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        const int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (valid && lane == leader) { old = wh[d]; wh[d] = old + __popc(peers); }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        __syncwarp();
+        if (key_out) { key_out[r] = key; rank_out[r] = old + __popc(peers & lt); }
+    }
+}
+
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, int shift, int bits,
+                                                             uint32_t* __restrict__ table, unsigned nblocks) {
+    __shared__ uint32_t s_hist[8 * RS_BINS];
+    const uint32_t mask = (1u << bits) - 1u;
+    rs_rank_tile(keys, n, (size_t)blockIdx.x * RS_TILE, shift, mask, s_hist, nullptr, nullptr);
+    __syncthreads();
+    const int d = threadIdx.x;   // RS_THREADS == RS_BINS
+    uint32_t c = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) c += s_hist[w * RS_BINS + d];
+    if (d < (1 << bits)) table[(size_t)d * nblocks + blockIdx.x] = c;
+}
+
+__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
+                                                                uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, size_t n,
+                                                                int shift, int bits, const uint32_t* __restrict__ table, unsigned nblocks) {
+    __shared__ uint32_t s_hist[8 * RS_BINS];
+    const uint32_t mask = (1u << bits) - 1u;
+    uint32_t key[RS_ITEMS], rank[RS_ITEMS];
+    const size_t tile_base = (size_t)blockIdx.x * RS_TILE;
+    rs_rank_tile(kin, n, tile_base, shift, mask, s_hist, key, rank);
+    __syncthreads();
+    {   // per-digit: global offset of this block's run, then exclusive prefix over the 8 warps
+        const int d = threadIdx.x;
+        uint32_t run = (d < (1 << bits)) ? table[(size_t)d * nblocks + blockIdx.x] : 0u;
+#pragma unroll
+        for (int w = 0; w < 8; w++) {
+            const uint32_t c = s_hist[w * RS_BINS + d];
+            s_hist[w * RS_BINS + d] = run;
+            run += c;
+        }
+    }
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const uint32_t* wb = s_hist + w * RS_BINS;
+    const size_t wbase = tile_base + (size_t)w * (32 * RS_ITEMS);
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; r++) {
+        const size_t i = wbase + (size_t)r * 32 + lane;
+        if (i < n) {
+            const uint32_t d = (key[r] >> shift) & mask;
+            const uint32_t pos = wb[d] + rank[r];
+            kout[pos] = key[r];
+            vout[pos] = vin[i];
+        }
+    }
+}
+
+void radix_pass_u32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, size_t n,
+                    int shift, int bits, uint32_t* table, uint32_t* scan_tmp, cudaStream_t st) {
+    if (n == 0) return;
+    const unsigned nb = (unsigned)rs_blocks(n);
+    const size_t tbl = (size_t)nb * (1u << bits);
+    rs_hist_kernel<<<nb, RS_THREADS, 0, st>>>(kin, n, shift, bits, table, nb);
+    scan_exclusive_u32(table, table, tbl, scan_tmp, nullptr, st);
+    rs_scatter_kernel<<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, table, nb);
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) gather_u32_kernel(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx,
+                                                         uint32_t* __restrict__ dst, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = __ldg(src + idx[i]);
+}
+void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, size_t n, cudaStream_t st) {
+    if (n == 0) return;
+    gather_u32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, idx, dst, n);
+}
+
+// duplicateWithKeys (rasterizer_impl.cu:78-126), walked in depth order; key = tile id only.
+__global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
+                                                        const uint32_t* __restrict__ tt_sorted, const float4* __restrict__ packed,
+                                                        const int* __restrict__ radii, int grid_x, int grid_y, int row_begin, int row_end,
+                                                        uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= P) return;
+    if (tt_sorted[i] == 0) return;
+    const uint32_t g = order[i];
+    const float4 a = __ldg(packed + 3 * (size_t)g);
+    uint32_t x0, y0, x1, y1;
+    get_rect(a.x, a.y, radii[g], (uint32_t)grid_x, (uint32_t)grid_y, x0, y0, x1, y1);
+    y0 = max(y0, (uint32_t)row_begin);
+    y1 = min(y1, (uint32_t)row_end);
+    uint32_t off = offsets[i];
+    for (uint32_t y = y0; y < y1; y++)
+        for (uint32_t x = x0; x < x1; x++) {
+            tile_keys[off] = y * (uint32_t)grid_x + x;
+            vals[off] = g;
+            off++;
+        }
+}
+
+void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, const uint32_t* tt_sorted,
+                      const float4* packed, const int* radii, int grid_x, int grid_y, int row_begin, int row_end,
+                      uint32_t* tile_keys, uint32_t* vals, cudaStream_t st) {
+    if (P <= 0) return;
+    duplicate_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
+                                                      row_begin, row_end, tile_keys, vals);
+}
+
+// identifyTileRanges (rasterizer_impl.cu:133-159); ranges are zeroed first (:377)
+__global__ void __launch_bounds__(256) tile_ranges_kernel(size_t R, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    const uint32_t cur = keys[i];
+    if (i == 0) ranges[cur].x = 0;
+    else {
+        const uint32_t prev = keys[i - 1];
+        if (cur != prev) {
+            ranges[prev].y = (uint32_t)i;
+            ranges[cur].x = (uint32_t)i;
+        }
+    }
+    if (i == R - 1) ranges[cur].y = (uint32_t)R;
+}
+
+void launch_tile_ranges(size_t R, const uint32_t* sorted_tile_keys, uint2* ranges, size_t tiles, cudaStream_t st) {
+    cudaMemsetAsync(ranges, 0, tiles * sizeof(uint2), st);
+    if (R == 0) return;
+    tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, sorted_tile_keys, ranges);
+}
+
+}  // namespace gsr

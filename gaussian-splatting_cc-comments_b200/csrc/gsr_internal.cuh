@@ -1,0 +1,170 @@
+// gsr_internal.cuh -- private declarations shared by the sm_100a kernels and the C-ABI layer.
+//
+// Buffer layouts here are private to this implementation (the three byte buffers are opaque
+// to callers, as in the reference: DGR/cuda_rasterizer/rasterizer_impl.h:33-81).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+
+#define GSR_TILE_X 16   // tile size is part of the observable contract (DGR config.h:16-17)
+#define GSR_TILE_Y 16
+#define GSR_TILE_PIX 256
+
+namespace gsr {
+
+// ---- per-Gaussian packed record consumed by both blending kernels (48 B, 3 x float4) ---------
+//   a = (mean2D.x, mean2D.y, conic.x, conic.y)
+//   b = (conic.z, opacity, r, g)
+//   c = (b, ext_x, ext_y, power_thr)
+// ext_x/ext_y: conservative half-extents (pixels) of the region where alpha can reach 1/255
+//              (negative => can never contribute); power_thr: `power < power_thr` implies
+//              alpha < 1/255 without evaluating exp.
+struct alignas(16) PackedRec { float4 a, b, c; };
+
+// ---- carve helpers ---------------------------------------------------------------------------
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct Carver {
+    char* base; size_t off;
+    explicit Carver(char* b) : base(b), off(0) {}
+    template <typename T> T* take(size_t count) {
+        off = align_up(off, 256);
+        T* p = base ? reinterpret_cast<T*>(base + off) : nullptr;
+        off += count * sizeof(T);
+        return p;
+    }
+};
+
+constexpr int RS_THREADS = 256;          // radix sort: threads per block
+constexpr int RS_ITEMS = 16;             // items per thread
+constexpr int RS_TILE = RS_THREADS * RS_ITEMS;   // 4096 items per block
+constexpr int RS_BINS = 256;             // 8-bit digits
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_ITEMS = 8;
+constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // 4096
+
+static inline size_t rs_blocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
+static inline size_t scan_blocks(size_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
+
+struct GeomState {
+    float4* packed;            // 3P float4
+    uint32_t* tiles_touched;   // P (band-clipped count)
+    uint8_t* clamped;          // P
+    uint32_t* keys[2];         // P each: depth bits (0xFFFFFFFF = emits nothing), ping-pong
+    uint32_t* vals[2];         // P each: Gaussian ids, ping-pong
+    uint32_t* tt_sorted;       // P: tiles_touched in depth order
+    uint32_t* offsets;         // P: exclusive scan of tt_sorted
+    uint32_t* table;           // rs_blocks(P) * RS_BINS
+    uint32_t* scan_tmp;        // block sums for the scans over P-sized / table-sized arrays
+    uint32_t* total;           // 1: num_rendered on the device
+    size_t bytes;
+    static GeomState carve(char* base, size_t P) {
+        GeomState g; Carver c(base);
+        g.packed = c.take<float4>(3 * P);
+        g.tiles_touched = c.take<uint32_t>(P);
+        g.clamped = c.take<uint8_t>(P);
+        g.keys[0] = c.take<uint32_t>(P); g.keys[1] = c.take<uint32_t>(P);
+        g.vals[0] = c.take<uint32_t>(P); g.vals[1] = c.take<uint32_t>(P);
+        g.tt_sorted = c.take<uint32_t>(P);
+        g.offsets = c.take<uint32_t>(P);
+        size_t tbl = rs_blocks(P) * RS_BINS;
+        g.table = c.take<uint32_t>(tbl);
+        size_t big = tbl > P ? tbl : P;
+        g.scan_tmp = c.take<uint32_t>(scan_blocks(big) + 1);
+        g.total = c.take<uint32_t>(1);
+        g.bytes = align_up(c.off, 256) + 256;
+        return g;
+    }
+};
+
+struct BinState {
+    uint32_t* vals[2];         // R each; vals[0] is the final point_list
+    uint32_t* keys[2];         // R each: tile ids, ping-pong
+    uint32_t* table;           // rs_blocks(R) * RS_BINS
+    uint32_t* scan_tmp;
+    size_t bytes;
+    static BinState carve(char* base, size_t R) {
+        BinState b; Carver c(base);
+        b.vals[0] = c.take<uint32_t>(R); b.vals[1] = c.take<uint32_t>(R);
+        b.keys[0] = c.take<uint32_t>(R); b.keys[1] = c.take<uint32_t>(R);
+        size_t tbl = rs_blocks(R) * RS_BINS;
+        b.table = c.take<uint32_t>(tbl);
+        b.scan_tmp = c.take<uint32_t>(scan_blocks(tbl) + 1);
+        b.bytes = align_up(c.off, 256) + 256;
+        return b;
+    }
+};
+
+struct ImageState {
+    float* final_T;            // N
+    uint32_t* n_contrib;       // N
+    uint2* ranges;             // tiles
+    size_t bytes;
+    static ImageState carve(char* base, size_t N, size_t tiles) {
+        ImageState s; Carver c(base);
+        s.final_T = c.take<float>(N);
+        s.n_contrib = c.take<uint32_t>(N);
+        s.ranges = c.take<uint2>(tiles);
+        s.bytes = align_up(c.off, 256) + 256;
+        return s;
+    }
+};
+
+// ---- stage launchers (each enqueues on `st`, none synchronises) --------------------------------
+struct Camera {             // device pointers, read once per block
+    const float* view; const float* proj; const float* campos;
+};
+
+struct PreprocessArgs {
+    int P, D, M;
+    const float* means3D; const float* scales; float scale_modifier; const float* rotations;
+    const float* opacities; const float* shs; const float* cov3D_precomp; const float* colors_precomp;
+    Camera cam;
+    int W, H; float tan_fovx, tan_fovy, focal_x, focal_y;
+    int grid_x, grid_y, row_begin, row_end;
+    int prefiltered;
+    int* radii;                // may alias an internal array
+    float4* packed; uint32_t* tiles_touched; uint8_t* clamped; uint32_t* depth_keys; uint32_t* ids;
+};
+void launch_preprocess(const PreprocessArgs& a, cudaStream_t st);
+void launch_mark_visible(int P, const float* means, const float* view, unsigned char* present, cudaStream_t st);
+
+// exclusive prefix sum of n uint32 (in may equal out); tmp holds scan_blocks(n)+1 words;
+// if total != nullptr the grand total is written there.
+void scan_exclusive_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t* tmp, uint32_t* total, cudaStream_t st);
+
+// one stable LSD pass on `bits` (<= 8) key bits starting at `shift`
+void radix_pass_u32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, size_t n,
+                    int shift, int bits, uint32_t* table, uint32_t* scan_tmp, cudaStream_t st);
+
+void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, size_t n, cudaStream_t st);
+
+void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, const uint32_t* tt_sorted,
+                      const float4* packed, const int* radii, int grid_x, int grid_y, int row_begin, int row_end,
+                      uint32_t* tile_keys, uint32_t* vals, cudaStream_t st);
+
+void launch_tile_ranges(size_t R, const uint32_t* sorted_tile_keys, uint2* ranges, size_t tiles, cudaStream_t st);
+
+void launch_render_forward(int grid_x, int row_begin, int row_end, const uint2* ranges, const uint32_t* point_list,
+                           int W, int H, const float4* packed, const float* bg, float* out_color,
+                           float* final_T, uint32_t* n_contrib, cudaStream_t st);
+
+void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2* ranges, const uint32_t* point_list,
+                            int W, int H, const float4* packed, const float* bg, const float* final_T,
+                            const uint32_t* n_contrib, const float* dL_dpix, float* grad_acc /* (P,12) */,
+                            cudaStream_t st);
+
+struct PreprocessBwdArgs {
+    int P, D, M;
+    const float* means3D; const int* radii; const float* shs; const uint8_t* clamped;
+    const float* scales; const float* rotations; float scale_modifier; const float* cov3D_precomp;
+    Camera cam;
+    int W, H; float tan_fovx, tan_fovy, focal_x, focal_y;
+    const float* grad_acc;     // (P,12)
+    float* dL_dmean2D; float* dL_dconic; float* dL_dopacity; float* dL_dcolor;
+    float* dL_dmean3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;
+};
+void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st);
+
+}  // namespace gsr

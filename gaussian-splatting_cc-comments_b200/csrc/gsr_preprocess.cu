@@ -1,0 +1,193 @@
+// gsr_preprocess.cu -- forward per-Gaussian stage for sm_100a.
+//
+// Replaces preprocessCUDA<3> (DGR/cuda_rasterizer/forward.cu:192-324) and checkFrustum
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:56-69).  One thread per Gaussian; HBM-bound
+// (P*(44+8) + P_vis*(12K+40) algorithmic bytes).  Differences from the
+// reference in structure (not in results):
+//   * camera matrices are staged once per block in shared memory,
+//   * SH coefficients are fetched as 16-byte vectors through the read-only path,
+//   * everything the blending kernels need is written as ONE 48-byte record per Gaussian
+//     (3 x st.v4) instead of five separate arrays, plus conservative cull extents,
+//   * cov3D is not stored (the backward recomputes it from scale/rotation),
+//   * the depth-sort key/value pair is emitted here.
+#include "gsr_internal.cuh"
+#include "gsr_math.cuh"
+#include <stdio.h>
+
+namespace gsr {
+
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+
+// colour from SH (forward.cu:21-81); vector path
+template <int DEG>
+__device__ __forceinline__ void sh_color_vec(const float* __restrict__ sh, const float* k, float* res) {
+    constexpr int K = (DEG + 1) * (DEG + 1);
+    constexpr int NF = 3 * K;
+    constexpr int NV = (NF + 3) / 4;
+#pragma unroll
+    for (int i = 0; i < NV; i++) {
+        const float4 v = ldg4(sh + 4 * i);
+        const float e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int f = 4 * i + j;
+            if (f < NF) {
+                const int kk = f / 3, ch = f % 3;
+                res[ch] = (kk == 0) ? mulr(e[j], k[0]) : fmar(k[kk], e[j], res[ch]);
+            }
+        }
+    }
+}
+
+__device__ __forceinline__ void sh_color_scalar(int K, const float* __restrict__ sh, const float* k, float* res) {
+    for (int ch = 0; ch < 3; ch++) res[ch] = mulr(__ldg(sh + ch), k[0]);
+    for (int kk = 1; kk < K; kk++)
+        for (int ch = 0; ch < 3; ch++) res[ch] = fmar(k[kk], __ldg(sh + 3 * kk + ch), res[ch]);
+}
+
+__global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
+    __shared__ float s_cam[36];
+    if (threadIdx.x < 16) s_cam[threadIdx.x] = a.cam.view[threadIdx.x];
+    else if (threadIdx.x < 32) s_cam[threadIdx.x] = a.cam.proj[threadIdx.x - 16];
+    else if (threadIdx.x < 35) s_cam[threadIdx.x] = a.cam.campos[threadIdx.x - 32];
+    __syncthreads();
+    const float* V = s_cam;
+    const float* Pm = s_cam + 16;
+
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.P) return;
+
+    int out_radius = 0;
+    uint32_t out_tiles = 0;
+    uint32_t out_key = 0xFFFFFFFFu;   // sorts behind every visible Gaussian; emits nothing
+
+    const float mx = __ldg(a.means3D + 3 * idx), my = __ldg(a.means3D + 3 * idx + 1), mz = __ldg(a.means3D + 3 * idx + 2);
+    // in_frustum (auxiliary.h:144-175): only the near-plane test is live
+    const float depth = dot4(V[2], V[6], V[10], V[14], mx, my, mz);
+    bool alive = !(depth <= 0.2f);
+    if (!alive && a.prefiltered) {
+        printf("Point is filtered although prefiltered is set. This shouldn't happen!");
+        __trap();
+    }
+    if (alive) {
+        const float hx = dot4(Pm[0], Pm[4], Pm[8], Pm[12], mx, my, mz);
+        const float hy = dot4(Pm[1], Pm[5], Pm[9], Pm[13], mx, my, mz);
+        const float hw = dot4(Pm[3], Pm[7], Pm[11], Pm[15], mx, my, mz);
+        const float p_w = __frcp_rn(addr(hw, 0.0000001f));
+        const float projx = mulr(hx, p_w), projy = mulr(hy, p_w);
+
+        float c3[6];
+        if (a.cov3D_precomp != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) c3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
+        } else {
+            float4 q;
+            if ((reinterpret_cast<uintptr_t>(a.rotations) & 15) == 0) q = ldg4(a.rotations + 4 * (size_t)idx);
+            else q = make_float4(__ldg(a.rotations + 4 * (size_t)idx), __ldg(a.rotations + 4 * (size_t)idx + 1),
+                                 __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
+            cov3d_from_scale_rot(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2),
+                                 a.scale_modifier, q, c3);
+        }
+        const EwaT e = ewa_T(mx, my, mz, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, V);
+        const float3 cov = ewa_cov2d(e, c3);
+        const float det = fmar(cov.x, cov.z, -mulr(cov.y, cov.y));
+        if (det != 0.0f) {
+            const float det_inv = __frcp_rn(det);
+            const float conx = mulr(cov.z, det_inv), cony = mulr(cov.y, -det_inv), conz = mulr(cov.x, det_inv);
+            const float mid = mulr(addr(cov.x, cov.z), 0.5f);
+            const float sq = __fsqrt_rn(fmaxf(fmar(mid, mid, -det), 0.1f));
+            const float lambda1 = addr(mid, sq), lambda2 = subr(mid, sq);
+            const float my_radius = ceilf(mulr(__fsqrt_rn(fmaxf(lambda1, lambda2)), 3.0f));
+            const int irad = __float2int_rz(my_radius);
+            const float px = ndc2pix(projx, a.W), py = ndc2pix(projy, a.H);
+            uint32_t x0, y0, x1, y1;
+            get_rect(px, py, irad, (uint32_t)a.grid_x, (uint32_t)a.grid_y, x0, y0, x1, y1);
+            if ((x1 - x0) * (y1 - y0) != 0) {
+                // ---- colour -------------------------------------------------------------------
+                float rgb[3];
+                uint32_t clampbits = 0;
+                if (a.colors_precomp == nullptr) {
+                    const float dx = subr(mx, V[32]), dy = subr(my, V[33]), dz = subr(mz, V[34]);
+                    const float len = __fsqrt_rn(fmar(dz, dz, fmar(dx, dx, mulr(dy, dy))));
+                    const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
+                    float k[16];
+                    sh_basis(a.D, x, y, z, k);
+                    const float* sh = a.shs + (size_t)idx * a.M * 3;
+                    const bool vec_ok = ((a.M * 3) % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
+                    float res[3] = {0.f, 0.f, 0.f};
+                    if (vec_ok && a.D == 3) sh_color_vec<3>(sh, k, res);
+                    else if (vec_ok && a.D == 2 && a.M * 3 >= 28) sh_color_vec<2>(sh, k, res);
+                    else if (vec_ok && a.D == 1) sh_color_vec<1>(sh, k, res);
+                    else if (vec_ok && a.D == 0) sh_color_vec<0>(sh, k, res);
+                    else sh_color_scalar((a.D + 1) * (a.D + 1), sh, k, res);
+#pragma unroll
+                    for (int ch = 0; ch < 3; ch++) {
+                        const float v = addr(res[ch], 0.5f);
+                        if (v < 0.0f) clampbits |= 1u << ch;
+                        rgb[ch] = (v < 0.0f) ? 0.0f : v;
+                    }
+                } else {
+#pragma unroll
+                    for (int ch = 0; ch < 3; ch++) rgb[ch] = __ldg(a.colors_precomp + 3 * (size_t)idx + ch);
+                }
+                const float opacity = __ldg(a.opacities + idx);
+
+                // ---- conservative cull data for the blending kernels ------------------------------
+                // alpha = min(.99, o*exp(power)) >= 1/255 needs power >= -ln(255 o).  The ellipse
+                // {q <= q0} has axis-aligned half extents sqrt(q0*cov.x), sqrt(q0*cov.z).  The extents
+                // are inflated for the rounding of `power` (cancellation grows with the anisotropy
+                // lambda1/lambda2), so a culled pair is always one the exact test would skip.
+                float ext_x = -1.0f, ext_y = -1.0f, thr = 1.0f;
+                const float o255 = opacity * 255.0f;
+                if (o255 > 1.0f) {   // NaN opacity -> never contributes in the reference either
+                    const float L = logf(o255);
+                    thr = -L - 1e-4f * L - 1e-4f;
+                    const float q0 = 2.0f * L * 1.0002f + 2e-4f;
+                    const float kappa = lambda1 / fmaxf(lambda2, 1e-12f);
+                    const float infl = 1.0f + 1e-3f + 2e-6f * kappa;
+                    ext_x = sqrtf(q0 * cov.x) * infl + 1e-2f;
+                    ext_y = sqrtf(q0 * cov.z) * infl + 1e-2f;
+                    if (!(ext_x == ext_x) || !(ext_y == ext_y)) { ext_x = 3.0e38f; ext_y = 3.0e38f; }
+                }
+                float4* rec = a.packed + 3 * (size_t)idx;
+                rec[0] = make_float4(px, py, conx, cony);
+                rec[1] = make_float4(conz, opacity, rgb[0], rgb[1]);
+                rec[2] = make_float4(rgb[2], ext_x, ext_y, thr);
+                a.clamped[idx] = (uint8_t)clampbits;
+
+                out_radius = irad;
+                // band-clipped tile count (tile-row sharded rendering); full grid by default
+                const uint32_t by0 = max(y0, (uint32_t)a.row_begin), by1 = min(y1, (uint32_t)a.row_end);
+                out_tiles = (by1 > by0) ? (by1 - by0) * (x1 - x0) : 0u;
+                if (out_tiles) out_key = __float_as_uint(depth);
+            }
+        }
+    }
+    if (a.radii) a.radii[idx] = out_radius;
+    a.tiles_touched[idx] = out_tiles;
+    a.depth_keys[idx] = out_key;
+    a.ids[idx] = (uint32_t)idx;
+}
+
+void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
+    if (a.P <= 0) return;
+    preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+}
+
+// rasterizer_impl.cu:56-69 (checkFrustum) -> present[idx] = p_view.z > 0.2 (auxiliary.h:165)
+__global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means,
+                                                           const float* __restrict__ view,
+                                                           unsigned char* __restrict__ present) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const float v2 = __ldg(view + 2), v6 = __ldg(view + 6), v10 = __ldg(view + 10), v14 = __ldg(view + 14);
+    const float depth = dot4(v2, v6, v10, v14, __ldg(means + 3 * idx), __ldg(means + 3 * idx + 1), __ldg(means + 3 * idx + 2));
+    present[idx] = !(depth <= 0.2f);
+}
+
+void launch_mark_visible(int P, const float* means, const float* view, unsigned char* present, cudaStream_t st) {
+    if (P <= 0) return;
+    mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means, view, present);
+}
+
+}  // namespace gsr

@@ -1,0 +1,151 @@
+/*
+ * gsr.h -- C ABI of the B200-native differentiable Gaussian-splatting rasterizer.
+ *
+ * This is the drop-in boundary underneath the reference's torch binding.  Each entry point
+ * replaces one static method of CudaRasterizer::Rasterizer
+ * (DGR = /root/reference/submodules/diff-gaussian-rasterization):
+ *
+ *   gsr_forward        <- Rasterizer::forward      DGR/cuda_rasterizer/rasterizer.h:31-55,
+ *                                                  impl DGR/cuda_rasterizer/rasterizer_impl.cu:227-411
+ *   gsr_backward       <- Rasterizer::backward     DGR/cuda_rasterizer/rasterizer.h:57-84,
+ *                                                  impl DGR/cuda_rasterizer/rasterizer_impl.cu:416-518
+ *   gsr_mark_visible   <- Rasterizer::markVisible  DGR/cuda_rasterizer/rasterizer.h:24-29,
+ *                                                  impl DGR/cuda_rasterizer/rasterizer_impl.cu:162-174
+ *   gsr_resize_fn      <- std::function<char*(size_t)> geometryBuffer/binningBuffer/imageBuffer
+ *                                                  DGR/cuda_rasterizer/rasterizer.h:32-34,
+ *                                                  made by resizeFunctional, DGR/rasterize_points.cu:28-36
+ *
+ * Plain C types only: device pointers, sizes, a cudaStream_t passed as void*.  All float
+ * arrays are fp32, contiguous, on the current CUDA device.  "Not provided" optional inputs are
+ * NULL, exactly as the reference's kernels test them (forward.cu:252,306; backward.cu:393,397).
+ * Every function returns 0 on success and a non-zero gsr_status otherwise; gsr_last_error()
+ * gives the text (thread-local).  Nothing here falls back to the CPU.
+ */
+#ifndef GSR_H_INCLUDED
+#define GSR_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GSR_VERSION 1
+
+typedef enum gsr_status {
+    GSR_OK = 0,
+    GSR_ERR_INVALID_ARGUMENT = 1, /* bad sizes / missing required pointer */
+    GSR_ERR_CUDA = 2,             /* a CUDA runtime call or (debug mode) a kernel failed */
+    GSR_ERR_ALLOC = 3             /* a resize callback returned NULL */
+} gsr_status;
+
+/* Growable scratch buffer: called once per forward with the number of bytes needed; must return
+ * a device pointer (>= 16-byte aligned) that stays valid until the matching backward is done. */
+typedef char* (*gsr_resize_fn)(void* user, size_t bytes);
+
+typedef struct gsr_forward_args {
+    int P;                       /* number of Gaussians */
+    int D;                       /* active SH degree 0..3 */
+    int M;                       /* SH coefficients per Gaussian in `shs` (0 if shs == NULL) */
+    const float* background;     /* (3) */
+    int width, height;
+    const float* means3D;        /* (P,3) */
+    const float* shs;            /* (P,M,3) or NULL */
+    const float* colors_precomp; /* (P,3) or NULL */
+    const float* opacities;      /* (P,1) */
+    const float* scales;         /* (P,3) or NULL */
+    float scale_modifier;
+    const float* rotations;      /* (P,4) or NULL */
+    const float* cov3D_precomp;  /* (P,6) or NULL */
+    const float* viewmatrix;     /* (4,4), flat index 4*col+row as auxiliary.h:60-79 reads it */
+    const float* projmatrix;     /* (4,4) */
+    const float* cam_pos;        /* (3) */
+    float tan_fovx, tan_fovy;
+    int prefiltered;
+    float* out_color;            /* (3,H,W) out; rows outside the tile-row band are left untouched */
+    int* radii;                  /* (P) out, may be NULL */
+    int debug;                   /* sync + check after every stage (CHECK_CUDA, auxiliary.h:177-184) */
+    /* Extension (not in the reference): restrict binning + blending to tile rows
+     * [tile_row_begin, tile_row_end) for tile-row sharded multi-GPU rendering.  0,0 = all rows.
+     * radii are computed on the full image either way. */
+    int tile_row_begin, tile_row_end;
+} gsr_forward_args;
+
+typedef struct gsr_backward_args {
+    int P, D, M, R;              /* R = num_rendered returned by the forward */
+    const float* background;
+    int width, height;
+    const float* means3D;
+    const float* shs;
+    const float* colors_precomp;
+    const float* scales;
+    float scale_modifier;
+    const float* rotations;
+    const float* cov3D_precomp;
+    const float* viewmatrix;
+    const float* projmatrix;
+    const float* cam_pos;
+    float tan_fovx, tan_fovy;
+    const int* radii;            /* (P) as written by the forward */
+    const char* geom_buffer;     /* the three buffers the forward filled, unchanged */
+    const char* binning_buffer;
+    const char* image_buffer;
+    const float* dL_dpix;        /* (3,H,W) */
+    /* Outputs.  Every element is written (no pre-zeroing needed), so callers may pass
+     * uninitialised memory -- the reference needs torch::zeros here (rasterize_points.cu:168-178). */
+    float* dL_dmean2D;           /* (P,3) */
+    float* dL_dconic;            /* (P,4) = (P,2,2), may be NULL (the reference does not return it) */
+    float* dL_dopacity;          /* (P,1) */
+    float* dL_dcolor;            /* (P,3) */
+    float* dL_dmean3D;           /* (P,3) */
+    float* dL_dcov3D;            /* (P,6) */
+    float* dL_dsh;               /* (P,M,3), NULL iff M == 0 */
+    float* dL_dscale;            /* (P,3) */
+    float* dL_drot;              /* (P,4) */
+    /* Scratch: (P,12) floats, 16-byte aligned, used for the per-Gaussian gradient accumulators
+     * the blending backward reduces into.  Zeroed internally. */
+    float* grad_scratch;
+    int debug;
+    int tile_row_begin, tile_row_end;
+} gsr_backward_args;
+
+/* Bytes needed for gsr_backward_args.grad_scratch */
+size_t gsr_backward_scratch_bytes(int P);
+
+/* Sizes of the three opaque buffers (what the resize callbacks will be asked for).
+ * kind: 0 = geometry (n = P), 1 = binning (n = R), 2 = image (n = width*height, aux = #tiles). */
+size_t gsr_required_bytes(int kind, size_t n, size_t aux);
+
+int gsr_forward(const gsr_forward_args* args,
+                gsr_resize_fn geometry_buffer, void* geometry_user,
+                gsr_resize_fn binning_buffer, void* binning_user,
+                gsr_resize_fn image_buffer, void* image_user,
+                void* cuda_stream, int* num_rendered);
+
+int gsr_backward(const gsr_backward_args* args, void* cuda_stream);
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     unsigned char* present /* (P) bool out */, void* cuda_stream);
+
+/* Introspection for tests (device pointers into the opaque buffers; layout is private otherwise) */
+typedef struct gsr_buffer_view {
+    const uint32_t* point_list;   /* (R)   sorted Gaussian ids, tile-major then depth            */
+    const uint32_t* ranges;       /* (T,2) start/end into point_list per tile                   */
+    const uint32_t* n_contrib;    /* (H*W)                                                      */
+    const float* final_T;         /* (H*W)                                                      */
+    const float* packed;          /* (P,12) x,y,conic.xyz,opacity,r,g,b,ext_x,ext_y,power_thr   */
+    const uint32_t* tiles_touched;/* (P)                                                        */
+    const uint8_t* clamped;       /* (P) bit c set = colour channel c was clamped at 0          */
+} gsr_buffer_view;
+
+int gsr_view_buffers(int P, int R, int width, int height, const char* geom_buffer,
+                     const char* binning_buffer, const char* image_buffer, gsr_buffer_view* out);
+
+const char* gsr_last_error(void);
+int gsr_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GSR_H_INCLUDED */

@@ -1,0 +1,56 @@
+#!/usr/bin/env python3
+"""Build the UNMODIFIED reference rasterizer (DGR) for sm_100 into oracle/_ref/.
+
+TEST / BENCH INFRASTRUCTURE ONLY -- nothing in the product path imports this.
+
+The reference's CUDA sources are compiled where they lie under
+/root/reference/submodules/diff-gaussian-rasterization (no copy of the sources
+enters this repository; oracle/_ref/ is git-ignored but travels to the GPU box
+with the snapshot).  Flags are the stock torch.utils.cpp_extension flags with
+TORCH_CUDA_ARCH_LIST=10.0 plus `-include cstdint` (rasterizer_impl.h uses
+std::uintptr_t without including <cstdint>, which gcc 13 no longer forgives).
+No -use_fast_math, matching the reference's setup.py:29.
+
+Result:  oracle/_ref/diff_gaussian_rasterization/{__init__.py,_C.so}
+         (the same layout `pip install --target` would give).
+"""
+import os, shutil, sys, glob
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF = "/root/reference/submodules/diff-gaussian-rasterization"
+OUT = os.path.join(HERE, "_ref")
+PKG = os.path.join(OUT, "diff_gaussian_rasterization")
+
+
+def build(verbose=False):
+    if not os.path.isdir(REF):
+        return False  # GPU box: only the prebuilt files exist
+    os.makedirs(PKG, exist_ok=True)
+    so = os.path.join(PKG, "_C.so")
+    srcs = [os.path.join(REF, p) for p in (
+        "cuda_rasterizer/rasterizer_impl.cu", "cuda_rasterizer/forward.cu",
+        "cuda_rasterizer/backward.cu", "rasterize_points.cu", "ext.cpp")]
+    newest = max(os.path.getmtime(s) for s in srcs)
+    if os.path.exists(so) and os.path.getmtime(so) >= newest:
+        return True
+    os.environ["TORCH_CUDA_ARCH_LIST"] = "10.0"
+    os.environ.setdefault("MAX_JOBS", "8")
+    from torch.utils.cpp_extension import load
+    bdir = os.path.join(OUT, "build")
+    os.makedirs(bdir, exist_ok=True)
+    load(name="_C", sources=srcs,
+         extra_include_paths=[os.path.join(REF, "third_party/glm")],
+         extra_cuda_cflags=["-include", "cstdint"],
+         build_directory=bdir, verbose=verbose, is_python_module=False)
+    built = glob.glob(os.path.join(bdir, "_C*.so"))
+    assert built, "reference build produced no .so"
+    shutil.copy2(built[0], so)
+    # the reference's Python wrapper, installed next to its extension (pip-install equivalent)
+    shutil.copy2(os.path.join(REF, "diff_gaussian_rasterization/__init__.py"),
+                 os.path.join(PKG, "__init__.py"))
+    return True
+
+
+if __name__ == "__main__":
+    ok = build(verbose="-v" in sys.argv)
+    print("reference build:", "ok" if ok else "skipped (no /root/reference)")
