@@ -1,0 +1,219 @@
+// gsr_api.cu -- C-ABI orchestration (include/gsr.h).
+//
+// Replaces CudaRasterizer::Rasterizer::{forward,backward,markVisible}
+// (DGR/cuda_rasterizer/rasterizer_impl.cu:162-174,227-411,416-518).  All work is enqueued on the
+// caller's stream (the reference uses the legacy default stream).  The one host sync per forward
+// -- reading num_rendered to size the binning buffer, rasterizer_impl.cu:331 -- is kept because
+// the API returns it as an int; it is a 4-byte async copy into pinned memory + stream sync.
+#include "../../include/gsr.h"
+#include "gsr_internal.cuh"
+#include <string>
+#include <cstdio>
+
+using namespace gsr;
+
+static thread_local std::string g_err;
+static thread_local uint32_t* g_pinned = nullptr;
+
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+
+#define GSR_CUDA(call)                                                                         \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess)                                                                 \
+            return fail(GSR_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e_));   \
+    } while (0)
+
+// CHECK_CUDA (auxiliary.h:177-184): with debug, sync and report the stage that failed
+#define GSR_STAGE(name, st, debug)                                                             \
+    do {                                                                                       \
+        cudaError_t e_ = cudaGetLastError();                                                   \
+        if (e_ == cudaSuccess && (debug)) e_ = cudaStreamSynchronize(st);                      \
+        if (e_ != cudaSuccess)                                                                 \
+            return fail(GSR_ERR_CUDA, std::string("stage ") + name + ": " + cudaGetErrorString(e_)); \
+    } while (0)
+
+static int bits_for(uint32_t n_values) {   // bits needed to represent ids 0..n_values-1
+    int b = 0;
+    while (b < 32 && (1ull << b) < (unsigned long long)n_values) b++;
+    return b;
+}
+
+extern "C" {
+
+const char* gsr_last_error(void) { return g_err.c_str(); }
+int gsr_version(void) { return GSR_VERSION; }
+
+size_t gsr_backward_scratch_bytes(int P) { return (size_t)(P > 0 ? P : 0) * 12 * sizeof(float) + 256; }
+
+size_t gsr_required_bytes(int kind, size_t n, size_t aux) {
+    switch (kind) {
+        case 0: return GeomState::carve(nullptr, n).bytes;
+        case 1: return BinState::carve(nullptr, n).bytes;
+        case 2: return ImageState::carve(nullptr, n, aux).bytes;
+        default: return 0;
+    }
+}
+
+int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                     unsigned char* present, void* cuda_stream) {
+    (void)projmatrix;   // the reference computes p_proj but only tests p_view.z (auxiliary.h:165)
+    if (P < 0) return fail(GSR_ERR_INVALID_ARGUMENT, "P < 0");
+    if (P == 0) return GSR_OK;
+    if (!means3D || !viewmatrix || !present) return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_mark_visible(P, means3D, viewmatrix, present, st);
+    GSR_STAGE("mark_visible", st, 0);
+    return GSR_OK;
+}
+
+int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_user, gsr_resize_fn bin_fn, void* bin_user,
+                gsr_resize_fn img_fn, void* img_user, void* cuda_stream, int* num_rendered) {
+    if (!a || !geom_fn || !bin_fn || !img_fn || !num_rendered) return fail(GSR_ERR_INVALID_ARGUMENT, "null argument");
+    *num_rendered = 0;
+    if (a->P < 0 || a->width <= 0 || a->height <= 0) return fail(GSR_ERR_INVALID_ARGUMENT, "bad sizes");
+    if (a->P == 0) return GSR_OK;     // rasterize_points.cu:94
+    if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->cam_pos || !a->background || !a->out_color)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "missing required pointer");
+    if (!a->colors_precomp && (!a->shs || a->M <= 0))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "provide SHs or precomputed colours");
+    if (!a->cov3D_precomp && (!a->scales || !a->rotations))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "provide scales+rotations or a precomputed 3D covariance");
+    if (a->shs && (a->D < 0 || a->D > 3 || (a->D + 1) * (a->D + 1) > a->M))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "SH degree does not fit M coefficients");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int P = a->P, W = a->width, H = a->height;
+    const int grid_x = (W + GSR_TILE_X - 1) / GSR_TILE_X, grid_y = (H + GSR_TILE_Y - 1) / GSR_TILE_Y;
+    int row_begin = 0, row_end = grid_y;
+    if (!(a->tile_row_begin == 0 && a->tile_row_end == 0)) {
+        row_begin = a->tile_row_begin; row_end = a->tile_row_end;
+        if (row_begin < 0 || row_end > grid_y || row_begin > row_end) return fail(GSR_ERR_INVALID_ARGUMENT, "bad tile row band");
+    }
+    const size_t tiles = (size_t)grid_x * grid_y;
+
+    char* gptr = geom_fn(geom_user, GeomState::carve(nullptr, P).bytes);
+    char* iptr = img_fn(img_user, ImageState::carve(nullptr, (size_t)W * H, tiles).bytes);
+    if (!gptr || !iptr) return fail(GSR_ERR_ALLOC, "resize callback returned NULL");
+    GeomState geom = GeomState::carve((char*)align_up((size_t)gptr, 256), P);
+    ImageState img = ImageState::carve((char*)align_up((size_t)iptr, 256), (size_t)W * H, tiles);
+    int* radii = a->radii ? a->radii : geom.radii_internal;
+
+    PreprocessArgs pa;
+    pa.P = P; pa.D = a->D; pa.M = a->M;
+    pa.means3D = a->means3D; pa.scales = a->scales; pa.scale_modifier = a->scale_modifier; pa.rotations = a->rotations;
+    pa.opacities = a->opacities; pa.shs = a->shs; pa.cov3D_precomp = a->cov3D_precomp; pa.colors_precomp = a->colors_precomp;
+    pa.cam.view = a->viewmatrix; pa.cam.proj = a->projmatrix; pa.cam.campos = a->cam_pos;
+    pa.W = W; pa.H = H; pa.tan_fovx = a->tan_fovx; pa.tan_fovy = a->tan_fovy;
+    pa.focal_y = H / (2.0f * a->tan_fovy);     // rasterizer_impl.cu:251-252
+    pa.focal_x = W / (2.0f * a->tan_fovx);
+    pa.grid_x = grid_x; pa.grid_y = grid_y; pa.row_begin = row_begin; pa.row_end = row_end;
+    pa.prefiltered = a->prefiltered;
+    pa.radii = radii; pa.packed = geom.packed; pa.tiles_touched = geom.tiles_touched; pa.clamped = geom.clamped;
+    pa.depth_keys = geom.keys[0]; pa.ids = geom.vals[0];
+    launch_preprocess(pa, st);
+    GSR_STAGE("preprocess", st, a->debug);
+
+    // depth order of the Gaussians: 4 stable 8-bit passes, result back in keys[0]/vals[0]
+    for (int pass = 0; pass < 4; pass++) {
+        const int s = pass & 1;
+        radix_pass_u32(geom.keys[s], geom.vals[s], geom.keys[s ^ 1], geom.vals[s ^ 1], P, 8 * pass, 8, geom.table, geom.scan_tmp, st);
+    }
+    GSR_STAGE("depth sort", st, a->debug);
+    launch_gather_u32(geom.tiles_touched, geom.vals[0], geom.tt_sorted, P, st);
+    scan_exclusive_u32(geom.tt_sorted, geom.offsets, P, geom.scan_tmp, geom.total, st);
+    GSR_STAGE("scan", st, a->debug);
+
+    if (!g_pinned) GSR_CUDA(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
+    GSR_CUDA(cudaMemcpyAsync(g_pinned, geom.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    GSR_CUDA(cudaStreamSynchronize(st));
+    const size_t R = *g_pinned;
+    if (R > 0x7fffffffull) return fail(GSR_ERR_INVALID_ARGUMENT, "num_rendered exceeds int range");
+
+    char* bptr = bin_fn(bin_user, BinState::carve(nullptr, R).bytes);
+    if (!bptr) return fail(GSR_ERR_ALLOC, "resize callback returned NULL");
+    BinState bin = BinState::carve((char*)align_up((size_t)bptr, 256), R);
+
+    const int tile_bits = bits_for((uint32_t)tiles);
+    const int npass = (tile_bits + 7) / 8;
+    int s = npass & 1;       // start so that the last pass lands in vals[0] == point_list
+    launch_duplicate(P, geom.vals[0], geom.offsets, geom.tt_sorted, geom.packed, radii, grid_x, grid_y, row_begin, row_end,
+                     bin.keys[s], bin.vals[s], st);
+    GSR_STAGE("duplicate", st, a->debug);
+    for (int pass = 0; pass < npass; pass++) {
+        const int bits = (tile_bits - 8 * pass) < 8 ? (tile_bits - 8 * pass) : 8;
+        radix_pass_u32(bin.keys[s], bin.vals[s], bin.keys[s ^ 1], bin.vals[s ^ 1], R, 8 * pass, bits, bin.table, bin.scan_tmp, st);
+        s ^= 1;
+    }
+    GSR_STAGE("tile sort", st, a->debug);
+    launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st);
+    GSR_STAGE("tile ranges", st, a->debug);
+    launch_render_forward(grid_x, row_begin, row_end, img.ranges, bin.vals[0], W, H, geom.packed, a->background,
+                          a->out_color, img.final_T, img.n_contrib, st);
+    GSR_STAGE("render", st, a->debug);
+    *num_rendered = (int)R;
+    return GSR_OK;
+}
+
+int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
+    if (!a) return fail(GSR_ERR_INVALID_ARGUMENT, "null argument");
+    if (a->P < 0 || a->R < 0 || a->width <= 0 || a->height <= 0) return fail(GSR_ERR_INVALID_ARGUMENT, "bad sizes");
+    if (a->P == 0) return GSR_OK;     // rasterize_points.cu:180
+    if (!a->means3D || !a->radii || !a->geom_buffer || !a->binning_buffer || !a->image_buffer || !a->dL_dpix ||
+        !a->viewmatrix || !a->projmatrix || !a->cam_pos || !a->background || !a->grad_scratch)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "missing required pointer");
+    if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dcolor || !a->dL_dmean3D || !a->dL_dcov3D || !a->dL_dscale || !a->dL_drot ||
+        (a->M > 0 && !a->dL_dsh))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "missing output pointer");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const int P = a->P, W = a->width, H = a->height;
+    const int grid_x = (W + GSR_TILE_X - 1) / GSR_TILE_X, grid_y = (H + GSR_TILE_Y - 1) / GSR_TILE_Y;
+    int row_begin = 0, row_end = grid_y;
+    if (!(a->tile_row_begin == 0 && a->tile_row_end == 0)) { row_begin = a->tile_row_begin; row_end = a->tile_row_end; }
+    if (row_begin < 0 || row_end > grid_y || row_begin > row_end) return fail(GSR_ERR_INVALID_ARGUMENT, "bad tile row band");
+    const size_t tiles = (size_t)grid_x * grid_y;
+    GeomState geom = GeomState::carve((char*)align_up((size_t)a->geom_buffer, 256), P);
+    BinState bin = BinState::carve((char*)align_up((size_t)a->binning_buffer, 256), (size_t)a->R);
+    ImageState img = ImageState::carve((char*)align_up((size_t)a->image_buffer, 256), (size_t)W * H, tiles);
+
+    float* acc = (float*)align_up((size_t)a->grad_scratch, 256);
+    GSR_CUDA(cudaMemsetAsync(acc, 0, (size_t)P * 12 * sizeof(float), st));
+    if (a->R > 0)
+        launch_render_backward(grid_x, row_begin, row_end, img.ranges, bin.vals[0], W, H, geom.packed, a->background,
+                               img.final_T, img.n_contrib, a->dL_dpix, acc, st);
+    GSR_STAGE("render backward", st, a->debug);
+
+    PreprocessBwdArgs pb;
+    pb.P = P; pb.D = a->D; pb.M = a->M;
+    pb.means3D = a->means3D; pb.radii = a->radii; pb.shs = a->shs; pb.clamped = geom.clamped;
+    pb.scales = a->scales; pb.rotations = a->rotations; pb.scale_modifier = a->scale_modifier; pb.cov3D_precomp = a->cov3D_precomp;
+    pb.cam.view = a->viewmatrix; pb.cam.proj = a->projmatrix; pb.cam.campos = a->cam_pos;
+    pb.W = W; pb.H = H; pb.tan_fovx = a->tan_fovx; pb.tan_fovy = a->tan_fovy;
+    pb.focal_y = H / (2.0f * a->tan_fovy);     // rasterizer_impl.cu:459-460
+    pb.focal_x = W / (2.0f * a->tan_fovx);
+    pb.grad_acc = acc;
+    pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dconic = a->dL_dconic; pb.dL_dopacity = a->dL_dopacity; pb.dL_dcolor = a->dL_dcolor;
+    pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh; pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
+    launch_preprocess_backward(pb, st);
+    GSR_STAGE("preprocess backward", st, a->debug);
+    return GSR_OK;
+}
+
+int gsr_view_buffers(int P, int R, int width, int height, const char* geom_buffer, const char* binning_buffer,
+                     const char* image_buffer, gsr_buffer_view* out) {
+    if (!out || P < 0 || R < 0 || width <= 0 || height <= 0) return fail(GSR_ERR_INVALID_ARGUMENT, "bad argument");
+    const int grid_x = (width + GSR_TILE_X - 1) / GSR_TILE_X, grid_y = (height + GSR_TILE_Y - 1) / GSR_TILE_Y;
+    GeomState geom = GeomState::carve(geom_buffer ? (char*)align_up((size_t)geom_buffer, 256) : nullptr, P);
+    BinState bin = BinState::carve(binning_buffer ? (char*)align_up((size_t)binning_buffer, 256) : nullptr, (size_t)R);
+    ImageState img = ImageState::carve(image_buffer ? (char*)align_up((size_t)image_buffer, 256) : nullptr, (size_t)width * height,
+                                       (size_t)grid_x * grid_y);
+    out->point_list = bin.vals[0];
+    out->ranges = reinterpret_cast<const uint32_t*>(img.ranges);
+    out->n_contrib = img.n_contrib;
+    out->final_T = img.final_T;
+    out->packed = reinterpret_cast<const float*>(geom.packed);
+    out->tiles_touched = geom.tiles_touched;
+    out->clamped = geom.clamped;
+    return GSR_OK;
+}
+
+}  // extern "C"

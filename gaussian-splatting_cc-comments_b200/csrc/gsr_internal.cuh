@@ -58,6 +58,7 @@ struct GeomState {
     uint32_t* table;           // rs_blocks(P) * RS_BINS
     uint32_t* scan_tmp;        // block sums for the scans over P-sized / table-sized arrays
     uint32_t* total;           // 1: num_rendered on the device
+    int* radii_internal;       // P: used when the caller passes radii == NULL (rasterizer_impl.cu:262-265)
     size_t bytes;
     static GeomState carve(char* base, size_t P) {
         GeomState g; Carver c(base);
@@ -73,6 +74,7 @@ struct GeomState {
         size_t big = tbl > P ? tbl : P;
         g.scan_tmp = c.take<uint32_t>(scan_blocks(big) + 1);
         g.total = c.take<uint32_t>(1);
+        g.radii_internal = c.take<int>(P);
         g.bytes = align_up(c.off, 256) + 256;
         return g;
     }

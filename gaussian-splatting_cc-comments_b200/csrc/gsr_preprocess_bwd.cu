@@ -1,0 +1,224 @@
+// gsr_preprocess_bwd.cu -- backward of the per-Gaussian stage for sm_100a.
+//
+// Fuses computeCov2DCUDA (DGR/cuda_rasterizer/backward.cu:144-277) and preprocessCUDA<3>
+// (backward) (:349-399, with computeColorFromSH :20-139 and computeCov3D :281-344) into one
+// kernel, one thread per Gaussian.  It reads the (P,12) gradient accumulators the blending
+// backward reduced into and WRITES every element of every output (zeros for Gaussians with
+// radii <= 0), so callers need no 300 B/Gaussian zero-fill (rasterize_points.cu:168-178).
+// cov3D is recomputed from scale/rotation with the forward's exact arithmetic instead of being
+// stored in the forward and re-read here.  HBM-bound.
+#include "gsr_internal.cuh"
+#include "gsr_math.cuh"
+
+namespace gsr {
+
+struct F3 { float x, y, z; };
+__device__ __forceinline__ F3 f3(float x, float y, float z) { F3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ F3 operator*(float s, F3 a) { return f3(s * a.x, s * a.y, s * a.z); }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return f3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ float dot(F3 a, F3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+
+// dnormvdv (auxiliary.h:109-120)
+__device__ __forceinline__ F3 dnormvdv(F3 v, F3 dv) {
+    const float sum2 = v.x * v.x + v.y * v.y + v.z * v.z;
+    const float invsum32 = 1.0f / sqrtf(sum2 * sum2 * sum2);
+    F3 r;
+    r.x = ((+sum2 - v.x * v.x) * dv.x - v.y * v.x * dv.y - v.z * v.x * dv.z) * invsum32;
+    r.y = (-v.x * v.y * dv.x + (sum2 - v.y * v.y) * dv.y - v.z * v.y * dv.z) * invsum32;
+    r.z = (-v.x * v.z * dv.x - v.y * v.z * dv.y + (sum2 - v.z * v.z) * dv.z) * invsum32;
+    return r;
+}
+
+// SH backward (backward.cu:20-139).  Writes dL_dsh[0..K) and returns dL/d(mean) through the
+// normalised view direction.
+__device__ __forceinline__ F3 sh_backward(int deg, const float* __restrict__ sh, F3 dir_orig, F3 dRGB, float* __restrict__ dL_dsh) {
+    const float len = __fsqrt_rn(fmar(dir_orig.z, dir_orig.z, fmar(dir_orig.x, dir_orig.x, mulr(dir_orig.y, dir_orig.y))));
+    const float x = __fdiv_rn(dir_orig.x, len), y = __fdiv_rn(dir_orig.y, len), z = __fdiv_rn(dir_orig.z, len);
+    float k[16];
+    sh_basis(deg, x, y, z, k);          // dRGB/dsh_k is the forward basis weight
+    const int K = (deg + 1) * (deg + 1);
+    for (int i = 0; i < K; i++) {
+        dL_dsh[3 * i] = k[i] * dRGB.x;
+        dL_dsh[3 * i + 1] = k[i] * dRGB.y;
+        dL_dsh[3 * i + 2] = k[i] * dRGB.z;
+    }
+    F3 dx = f3(0, 0, 0), dy = f3(0, 0, 0), dz = f3(0, 0, 0);
+#define SHC(i) f3(__ldg(sh + 3 * (i)), __ldg(sh + 3 * (i) + 1), __ldg(sh + 3 * (i) + 2))
+    if (deg > 0) {
+        const F3 s1 = SHC(1), s2 = SHC(2), s3 = SHC(3);
+        dx = -GSR_SH_C1 * s3;
+        dy = -GSR_SH_C1 * s1;
+        dz = GSR_SH_C1 * s2;
+        if (deg > 1) {
+            const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+            const F3 s4 = SHC(4), s5 = SHC(5), s6 = SHC(6), s7 = SHC(7), s8 = SHC(8);
+            dx = dx + (GSR_SH_C2_0 * y * s4 + GSR_SH_C2_2 * 2.f * -x * s6 + GSR_SH_C2_3 * z * s7 + GSR_SH_C2_4 * 2.f * x * s8);
+            dy = dy + (GSR_SH_C2_0 * x * s4 + GSR_SH_C2_1 * z * s5 + GSR_SH_C2_2 * 2.f * -y * s6 + GSR_SH_C2_4 * 2.f * -y * s8);
+            dz = dz + (GSR_SH_C2_1 * y * s5 + GSR_SH_C2_2 * 2.f * 2.f * z * s6 + GSR_SH_C2_3 * x * s7);
+            if (deg > 2) {
+                const F3 s9 = SHC(9), s10 = SHC(10), s11 = SHC(11), s12 = SHC(12), s13 = SHC(13), s14 = SHC(14), s15 = SHC(15);
+                dx = dx + (GSR_SH_C3_0 * 3.f * 2.f * xy * s9 + GSR_SH_C3_1 * yz * s10 + GSR_SH_C3_2 * -2.f * xy * s11 +
+                           GSR_SH_C3_3 * -3.f * 2.f * xz * s12 + GSR_SH_C3_4 * (-3.f * xx + 4.f * zz - yy) * s13 +
+                           GSR_SH_C3_5 * 2.f * xz * s14 + GSR_SH_C3_6 * 3.f * (xx - yy) * s15);
+                dy = dy + (GSR_SH_C3_0 * 3.f * (xx - yy) * s9 + GSR_SH_C3_1 * xz * s10 + GSR_SH_C3_2 * (-3.f * yy + 4.f * zz - xx) * s11 +
+                           GSR_SH_C3_3 * -3.f * 2.f * yz * s12 + GSR_SH_C3_4 * -2.f * xy * s13 + GSR_SH_C3_5 * -2.f * yz * s14 +
+                           GSR_SH_C3_6 * -3.f * 2.f * xy * s15);
+                dz = dz + (GSR_SH_C3_1 * xy * s10 + GSR_SH_C3_2 * 4.f * 2.f * yz * s11 + GSR_SH_C3_3 * 3.f * (2.f * zz - xx - yy) * s12 +
+                           GSR_SH_C3_4 * 4.f * 2.f * xz * s13 + GSR_SH_C3_5 * (xx - yy) * s14);
+            }
+        }
+    }
+#undef SHC
+    const F3 dL_ddir = f3(dot(dx, dRGB), dot(dy, dRGB), dot(dz, dRGB));
+    return dnormvdv(dir_orig, dL_ddir);
+}
+
+// computeCov3D backward (backward.cu:281-344)
+__device__ __forceinline__ void cov3d_backward(float sx0, float sy0, float sz0, float mod, float4 q, const float* g /* dL_dcov3D[6] */,
+                                               float* dL_dscale, float* dL_drot) {
+    const float r = q.x, x = q.y, y = q.z, z = q.w;
+    // R[c][r] as GLM columns
+    const float R[3][3] = {{1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y)},
+                           {2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x)},
+                           {2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y)}};
+    const float s[3] = {mod * sx0, mod * sy0, mod * sz0};
+    const float dS[3][3] = {{g[0], 0.5f * g[1], 0.5f * g[2]}, {0.5f * g[1], g[3], 0.5f * g[4]}, {0.5f * g[2], 0.5f * g[4], g[5]}};
+    // M[j][i] = s_i * R[j][i];  dL_dM[j][i] = sum_k 2*M[k][i]*dS[j][k]
+    float dM[3][3];
+#pragma unroll
+    for (int j = 0; j < 3; j++)
+#pragma unroll
+        for (int i = 0; i < 3; i++)
+            dM[j][i] = 2.0f * (s[i] * R[0][i]) * dS[j][0] + 2.0f * (s[i] * R[1][i]) * dS[j][1] + 2.0f * (s[i] * R[2][i]) * dS[j][2];
+    // dL_dscale_k = dot(Rt[k], dL_dMt[k]) = sum_m R[m][k] * dM[m][k]
+#pragma unroll
+    for (int k = 0; k < 3; k++) dL_dscale[k] = R[0][k] * dM[0][k] + R[1][k] * dM[1][k] + R[2][k] * dM[2][k];
+    // D(i,j) = dL_dMt[i][j] * s_i = dM[j][i] * s_i
+#define D(i, j) (dM[j][i] * s[i])
+    dL_drot[0] = 2 * z * (D(0, 1) - D(1, 0)) + 2 * y * (D(2, 0) - D(0, 2)) + 2 * x * (D(1, 2) - D(2, 1));
+    dL_drot[1] = 2 * y * (D(1, 0) + D(0, 1)) + 2 * z * (D(2, 0) + D(0, 2)) + 2 * r * (D(1, 2) - D(2, 1)) - 4 * x * (D(2, 2) + D(1, 1));
+    dL_drot[2] = 2 * x * (D(1, 0) + D(0, 1)) + 2 * r * (D(2, 0) - D(0, 2)) + 2 * z * (D(1, 2) + D(2, 1)) - 4 * y * (D(2, 2) + D(0, 0));
+    dL_drot[3] = 2 * r * (D(0, 1) - D(1, 0)) + 2 * x * (D(2, 0) + D(0, 2)) + 2 * y * (D(1, 2) + D(2, 1)) - 4 * z * (D(1, 1) + D(0, 0));
+#undef D
+}
+
+__global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreprocessBwdArgs a) {
+    __shared__ float s_cam[36];
+    if (threadIdx.x < 16) s_cam[threadIdx.x] = a.cam.view[threadIdx.x];
+    else if (threadIdx.x < 32) s_cam[threadIdx.x] = a.cam.proj[threadIdx.x - 16];
+    else if (threadIdx.x < 35) s_cam[threadIdx.x] = a.cam.campos[threadIdx.x - 32];
+    __syncthreads();
+    const float* V = s_cam;
+    const float* Pm = s_cam + 16;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.P) return;
+    const size_t i3 = 3 * (size_t)idx;
+
+    float dmean[3] = {0, 0, 0}, dcov[6] = {0, 0, 0, 0, 0, 0}, dscale[3] = {0, 0, 0}, drot[4] = {0, 0, 0, 0};
+    float g[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    const bool visible = a.radii[idx] > 0;
+    float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
+    int sh_written = 0;
+    if (visible) {
+        const float4* ga = reinterpret_cast<const float4*>(a.grad_acc + 12 * (size_t)idx);
+        const float4 g0 = ga[0], g1 = ga[1];
+        g[0] = g0.x; g[1] = g0.y; g[2] = g0.z; g[3] = g0.w; g[4] = g1.x; g[5] = g1.y; g[6] = g1.z; g[7] = g1.w;
+        g[8] = a.grad_acc[12 * (size_t)idx + 8];
+        const float mx = __ldg(a.means3D + i3), my = __ldg(a.means3D + i3 + 1), mz = __ldg(a.means3D + i3 + 2);
+        float c3[6];
+        float4 q = make_float4(0, 0, 0, 0);
+        float sx = 0, sy = 0, sz = 0;
+        if (a.cov3D_precomp != nullptr) {
+#pragma unroll
+            for (int i = 0; i < 6; i++) c3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
+        } else {
+            q = make_float4(__ldg(a.rotations + 4 * (size_t)idx), __ldg(a.rotations + 4 * (size_t)idx + 1),
+                            __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
+            sx = __ldg(a.scales + i3); sy = __ldg(a.scales + i3 + 1); sz = __ldg(a.scales + i3 + 2);
+            cov3d_from_scale_rot(sx, sy, sz, a.scale_modifier, q, c3);
+        }
+        // ---- computeCov2DCUDA (backward.cu:144-277) ----
+        const EwaT e = ewa_T(mx, my, mz, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, V);
+        const float3 cov = ewa_cov2d(e, c3);
+        const float limx = 1.3f * a.tan_fovx, limy = 1.3f * a.tan_fovy;
+        const float txtz = e.tx / e.tz, tytz = e.ty / e.tz;
+        const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
+        const float y_grad_mul = (tytz < -limy || tytz > limy) ? 0.f : 1.f;
+        const float tcx = e.cx * e.tz, tcy = e.cy * e.tz;       // clamped t.x, t.y
+        const float ca = cov.x, cb = cov.y, cc = cov.z;
+        const float denom = ca * cc - cb * cb;
+        float dL_da = 0, dL_db = 0, dL_dc = 0;
+        const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+        const float dcx = g[2], dcy = g[3], dcz = g[4];           // dL_dconic .x .y .w
+        if (denom2inv != 0) {
+            dL_da = denom2inv * (-cc * cc * dcx + 2 * cb * cc * dcy + (denom - ca * cc) * dcz);
+            dL_dc = denom2inv * (-ca * ca * dcz + 2 * ca * cb * dcy + (denom - ca * cc) * dcx);
+            dL_db = denom2inv * 2 * (cb * cc * dcx - (denom + 2 * cb * cb) * dcy + ca * cb * dcz);
+            dcov[0] = (e.T00 * e.T00 * dL_da + e.T00 * e.T10 * dL_db + e.T10 * e.T10 * dL_dc);
+            dcov[3] = (e.T01 * e.T01 * dL_da + e.T01 * e.T11 * dL_db + e.T11 * e.T11 * dL_dc);
+            dcov[5] = (e.T02 * e.T02 * dL_da + e.T02 * e.T12 * dL_db + e.T12 * e.T12 * dL_dc);
+            dcov[1] = 2 * e.T00 * e.T01 * dL_da + (e.T00 * e.T11 + e.T01 * e.T10) * dL_db + 2 * e.T10 * e.T11 * dL_dc;
+            dcov[2] = 2 * e.T00 * e.T02 * dL_da + (e.T00 * e.T12 + e.T02 * e.T10) * dL_db + 2 * e.T10 * e.T12 * dL_dc;
+            dcov[4] = 2 * e.T02 * e.T01 * dL_da + (e.T01 * e.T12 + e.T02 * e.T11) * dL_db + 2 * e.T11 * e.T12 * dL_dc;
+        }
+        const float p0 = e.T00 * c3[0] + e.T01 * c3[1] + e.T02 * c3[2];
+        const float p1 = e.T00 * c3[1] + e.T01 * c3[3] + e.T02 * c3[4];
+        const float p2 = e.T00 * c3[2] + e.T01 * c3[4] + e.T02 * c3[5];
+        const float q0 = e.T10 * c3[0] + e.T11 * c3[1] + e.T12 * c3[2];
+        const float q1 = e.T10 * c3[1] + e.T11 * c3[3] + e.T12 * c3[4];
+        const float q2 = e.T10 * c3[2] + e.T11 * c3[4] + e.T12 * c3[5];
+        const float dT00 = 2 * p0 * dL_da + q0 * dL_db, dT01 = 2 * p1 * dL_da + q1 * dL_db, dT02 = 2 * p2 * dL_da + q2 * dL_db;
+        const float dT10 = 2 * q0 * dL_dc + p0 * dL_db, dT11 = 2 * q1 * dL_dc + p1 * dL_db, dT12 = 2 * q2 * dL_dc + p2 * dL_db;
+        const float dJ00 = V[0] * dT00 + V[4] * dT01 + V[8] * dT02;
+        const float dJ02 = V[2] * dT00 + V[6] * dT01 + V[10] * dT02;
+        const float dJ11 = V[1] * dT10 + V[5] * dT11 + V[9] * dT12;
+        const float dJ12 = V[2] * dT10 + V[6] * dT11 + V[10] * dT12;
+        const float tz = 1.f / e.tz, tz2 = tz * tz, tz3 = tz2 * tz;
+        const float h_x = a.focal_x, h_y = a.focal_y;
+        const float dtx = x_grad_mul * -h_x * tz2 * dJ02;
+        const float dty = y_grad_mul * -h_y * tz2 * dJ12;
+        const float dtz = -h_x * tz2 * dJ00 - h_y * tz2 * dJ11 + (2 * h_x * tcx) * tz3 * dJ02 + (2 * h_y * tcy) * tz3 * dJ12;
+        dmean[0] = V[0] * dtx + V[1] * dty + V[2] * dtz;          // transformVec4x3Transpose
+        dmean[1] = V[4] * dtx + V[5] * dty + V[6] * dtz;
+        dmean[2] = V[8] * dtx + V[9] * dty + V[10] * dtz;
+        // ---- preprocessCUDA backward: projection part (backward.cu:373-390) ----
+        const float m_w = 1.0f / ((Pm[3] * mx + Pm[7] * my + Pm[11] * mz + Pm[15]) + 0.0000001f);
+        const float mul1 = (Pm[0] * mx + Pm[4] * my + Pm[8] * mz + Pm[12]) * m_w * m_w;
+        const float mul2 = (Pm[1] * mx + Pm[5] * my + Pm[9] * mz + Pm[13]) * m_w * m_w;
+        dmean[0] += (Pm[0] * m_w - Pm[3] * mul1) * g[0] + (Pm[1] * m_w - Pm[3] * mul2) * g[1];
+        dmean[1] += (Pm[4] * m_w - Pm[7] * mul1) * g[0] + (Pm[5] * m_w - Pm[7] * mul2) * g[1];
+        dmean[2] += (Pm[8] * m_w - Pm[11] * mul1) * g[0] + (Pm[9] * m_w - Pm[11] * mul2) * g[1];
+        // ---- SH (backward.cu:392-394) ----
+        if (a.shs != nullptr) {
+            const uint32_t cl = a.clamped[idx];
+            const F3 dRGB = f3((cl & 1) ? 0.f : g[6], (cl & 2) ? 0.f : g[7], (cl & 4) ? 0.f : g[8]);
+            const F3 dir = f3(subr(mx, V[32]), subr(my, V[33]), subr(mz, V[34]));
+            const F3 dm = sh_backward(a.D, a.shs + (size_t)idx * a.M * 3, dir, dRGB, dsh);
+            sh_written = (a.D + 1) * (a.D + 1);
+            dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
+        }
+        // ---- scale / rotation (backward.cu:396-398) ----
+        if (a.scales != nullptr) cov3d_backward(sx, sy, sz, a.scale_modifier, q, dcov, dscale, drot);
+    }
+    // ---- write everything (zeros where the reference's pre-zeroed tensors stay untouched) ----
+    a.dL_dmean2D[i3] = g[0]; a.dL_dmean2D[i3 + 1] = g[1]; a.dL_dmean2D[i3 + 2] = 0.f;
+    if (a.dL_dconic) {
+        reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(g[2], g[3], 0.f, g[4]);
+    }
+    a.dL_dopacity[idx] = g[5];
+    a.dL_dcolor[i3] = g[6]; a.dL_dcolor[i3 + 1] = g[7]; a.dL_dcolor[i3 + 2] = g[8];
+    a.dL_dmean3D[i3] = dmean[0]; a.dL_dmean3D[i3 + 1] = dmean[1]; a.dL_dmean3D[i3 + 2] = dmean[2];
+#pragma unroll
+    for (int i = 0; i < 6; i++) a.dL_dcov3D[6 * (size_t)idx + i] = dcov[i];
+    a.dL_dscale[i3] = dscale[0]; a.dL_dscale[i3 + 1] = dscale[1]; a.dL_dscale[i3 + 2] = dscale[2];
+#pragma unroll
+    for (int i = 0; i < 4; i++) a.dL_drot[4 * (size_t)idx + i] = drot[i];
+    if (dsh) for (int i = 3 * sh_written; i < 3 * a.M; i++) dsh[i] = 0.f;
+}
+
+void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
+    if (a.P <= 0) return;
+    preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+}
+
+}  // namespace gsr

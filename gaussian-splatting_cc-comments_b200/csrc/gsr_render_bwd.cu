@@ -1,0 +1,184 @@
+// gsr_render_bwd.cu -- backward of the per-tile alpha blending for sm_100a.
+//
+// Replaces renderCUDA<3> (backward) (DGR/cuda_rasterizer/backward.cu:408-601), which issues nine
+// scalar float atomicAdd per (pixel, Gaussian) pair.  Here:
+//   * the tile is replayed back to front starting at the tile's LAST contributor (block max of
+//     n_contrib) instead of at the end of the tile's list;
+//   * each warp owns an 8x4 pixel block and culls staged Gaussians against it exactly as the
+//     forward does (same extents, same `power < thr` skip, so the same pairs are blended);
+//   * the nine per-pair gradient terms are reduced across the warp with a shuffle
+//     reduce-scatter (8 values in 9 shuffles + 1 value in 5) and leave as ONE 8-lane
+//     red.global.add.f32 on consecutive addresses + one scalar red, into a (P,12) float scratch
+//     that the preprocess backward consumes;
+// Per-pixel replay order (the T division chain, backward.cu:534) is unchanged; only the
+// cross-pixel summation order differs (gradient tolerance 1e-4 relative L2).
+#include "gsr_internal.cuh"
+#include "gsr_math.cuh"
+
+namespace gsr {
+
+constexpr int RBB = GSR_TILE_PIX;
+
+template <int N>
+__device__ __forceinline__ void reduce_scatter_step(float* v, int bit, bool upper) {
+#pragma unroll
+    for (int k = 0; k < N / 2; k++) {
+        const float send = upper ? v[k] : v[k + N / 2];
+        const float keep = upper ? v[k + N / 2] : v[k];
+        v[k] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+    }
+}
+
+__global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                                                         int W, int H, int grid_x, int row_begin,
+                                                         const float4* __restrict__ packed, const float* __restrict__ bg,
+                                                         const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
+                                                         const float* __restrict__ dL_dpixels, float* __restrict__ grad_acc) {
+    __shared__ float4 s_a[RBB];
+    __shared__ float4 s_b[RBB];
+    __shared__ float4 s_c[RBB];
+    __shared__ uint32_t s_id[RBB];
+    __shared__ uint32_t s_max[8];
+
+    const int tile_x = blockIdx.x, tile_y = blockIdx.y + row_begin;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int bx0 = tile_x * GSR_TILE_X + (warp & 1) * 8;
+    const int by0 = tile_y * GSR_TILE_Y + (warp >> 1) * 4;
+    const int pix_x = bx0 + (lane & 7), pix_y = by0 + (lane >> 3);
+    const bool inside = pix_x < W && pix_y < H;
+    const float pixfx = (float)pix_x, pixfy = (float)pix_y;
+    const float fx0 = (float)bx0, fx1 = (float)(bx0 + 7), fy0 = (float)by0, fy1 = (float)(by0 + 3);
+    const size_t pix_id = (size_t)pix_y * W + pix_x;
+    const size_t HW = (size_t)H * W;
+
+    const uint2 range = ranges[tile_y * grid_x + tile_x];
+
+    const float T_final = inside ? final_Ts[pix_id] : 0.0f;
+    float T = T_final;
+    const int last_contributor = inside ? (int)n_contrib[pix_id] : 0;
+    float dpix0 = 0.f, dpix1 = 0.f, dpix2 = 0.f;
+    if (inside) {
+        dpix0 = dL_dpixels[pix_id];
+        dpix1 = dL_dpixels[HW + pix_id];
+        dpix2 = dL_dpixels[2 * HW + pix_id];
+    }
+    const float bg_dot_dpixel = __ldg(bg) * dpix0 + __ldg(bg + 1) * dpix1 + __ldg(bg + 2) * dpix2;
+    float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f;       // accum_rec
+    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;       // last_color
+    float last_alpha = 0.f;
+    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
+
+    // block / warp maxima of the last contributor: nothing behind them has a gradient
+    const int wmax = (int)__reduce_max_sync(0xffffffffu, (uint32_t)last_contributor);
+    if (lane == 0) s_max[warp] = (uint32_t)wmax;
+    __syncthreads();
+    int bmax = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) bmax = max(bmax, (int)s_max[w]);
+    const int rounds = (bmax + RBB - 1) / RBB;
+
+    for (int i = 0; i < rounds; i++) {
+        __syncthreads();
+        const int first_pos = bmax - 1 - i * RBB;          // position staged by thread 0
+        const int mypos = first_pos - (int)threadIdx.x;
+        if (mypos >= 0) {
+            const uint32_t id = point_list[range.x + mypos];
+            const float4* rec = packed + 3 * (size_t)id;
+            s_id[threadIdx.x] = id;
+            s_a[threadIdx.x] = __ldg(rec);
+            s_b[threadIdx.x] = __ldg(rec + 1);
+            s_c[threadIdx.x] = __ldg(rec + 2);
+        }
+        __syncthreads();
+        const int count = min(RBB, first_pos + 1);
+        if (first_pos - (count - 1) >= wmax) continue;      // whole batch is behind this warp's last contributor
+        for (int cbase = 0; cbase < count; cbase += 32) {
+            const int jj = cbase + lane;
+            bool hit = false;
+            if (jj < count && first_pos - jj < wmax) {
+                const float4 a = s_a[jj];
+                const float4 c = s_c[jj];
+                const float ddx = fmaxf(fmaxf(fx0 - a.x, a.x - fx1), 0.0f);
+                const float ddy = fmaxf(fmaxf(fy0 - a.y, a.y - fy1), 0.0f);
+                hit = (ddx <= c.y) && (ddy <= c.z);
+            }
+            uint32_t m = __ballot_sync(0xffffffffu, hit);
+            while (m) {
+                const int j = cbase + (__ffs(m) - 1);
+                m &= m - 1;
+                const int pos = first_pos - j;
+                const float4 a = s_a[j];
+                const float4 b = s_b[j];
+                const float4 c = s_c[j];
+                float v[8];
+                float v8 = 0.f;
+#pragma unroll
+                for (int q = 0; q < 8; q++) v[q] = 0.f;
+                bool contrib = false;
+                if (pos < last_contributor) {
+                    // same expression as the forward, so the same pairs pass the tests
+                    const float dx = subr(a.x, pixfx), dy = subr(a.y, pixfy);
+                    const float s = fmar(dx, mulr(dx, a.z), mulr(dy, mulr(dy, b.x)));
+                    const float power = fmar(s, -0.5f, -mulr(dy, mulr(dx, a.w)));
+                    if (!(power > 0.0f) && !(power < c.w)) {
+                        const float G = expf(power);
+                        const float alpha = fminf(0.99f, mulr(b.y, G));
+                        if (!(alpha < 1.0f / 255.0f)) {
+                            contrib = true;
+                            const float one_m_alpha = 1.0f - alpha;
+                            const float inv = __frcp_rn(one_m_alpha);
+                            T = T * inv;                                   // backward.cu:534
+                            const float dchannel_dcolor = alpha * T;
+                            // backward.cu:542-562
+                            ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0;
+                            ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1;
+                            ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2;
+                            lc0 = b.z; lc1 = b.w; lc2 = c.x;
+                            float dL_dalpha = (lc0 - ar0) * dpix0 + (lc1 - ar1) * dpix1 + (lc2 - ar2) * dpix2;
+                            v[6] = dchannel_dcolor * dpix0;
+                            v[7] = dchannel_dcolor * dpix1;
+                            v8 = dchannel_dcolor * dpix2;
+                            dL_dalpha *= T;
+                            last_alpha = alpha;
+                            dL_dalpha += (-T_final * inv) * bg_dot_dpixel;  // backward.cu:571-574
+                            const float dL_dG = b.y * dL_dalpha;
+                            const float gdx = G * dx, gdy = G * dy;
+                            const float dG_ddelx = -gdx * a.z - gdy * a.w;
+                            const float dG_ddely = -gdy * b.x - gdx * a.w;
+                            v[0] = dL_dG * dG_ddelx * ddelx_dx;             // backward.cu:587-598
+                            v[1] = dL_dG * dG_ddely * ddely_dy;
+                            v[2] = -0.5f * gdx * dx * dL_dG;
+                            v[3] = -0.5f * gdx * dy * dL_dG;
+                            v[4] = -0.5f * gdy * dy * dL_dG;
+                            v[5] = G * dL_dalpha;
+                        }
+                    }
+                }
+                if (__any_sync(0xffffffffu, contrib)) {
+                    reduce_scatter_step<8>(v, 16, (lane & 16) != 0);
+                    reduce_scatter_step<4>(v, 8, (lane & 8) != 0);
+                    reduce_scatter_step<2>(v, 4, (lane & 4) != 0);
+                    float r = v[0];
+                    r += __shfl_xor_sync(0xffffffffu, r, 2);
+                    r += __shfl_xor_sync(0xffffffffu, r, 1);
+#pragma unroll
+                    for (int d = 16; d > 0; d >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, d);
+                    float* dst = grad_acc + 12 * (size_t)s_id[j];
+                    if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), r);
+                    else if (lane == 1) atomicAdd(dst + 8, v8);
+                }
+            }
+        }
+    }
+}
+
+void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2* ranges, const uint32_t* point_list,
+                            int W, int H, const float4* packed, const float* bg, const float* final_T,
+                            const uint32_t* n_contrib, const float* dL_dpix, float* grad_acc, cudaStream_t st) {
+    if (row_end <= row_begin || grid_x <= 0) return;
+    dim3 grid(grid_x, row_end - row_begin, 1);
+    render_bwd_kernel<<<grid, 256, 0, st>>>(ranges, point_list, W, H, grid_x, row_begin, packed, bg, final_T, n_contrib,
+                                             dL_dpix, grad_acc);
+}
+
+}  // namespace gsr

@@ -1,0 +1,186 @@
+// torch_binding.cpp -- the `_C` extension module: a thin torch layer over the C ABI (include/gsr.h).
+//
+// Same three entry points, argument order and return tuples as the reference's pybind module
+// (DGR/ext.cpp:18-22, DGR/rasterize_points.h:18-67, DGR/rasterize_points.cu:38-237).  Differences:
+// a CUDAGuard on means3D's device and the CURRENT torch stream are used (the reference runs on
+// the legacy default stream of the current device); gradient outputs are views into ONE flat
+// buffer (handy for a single NCCL all-reduce) that the kernels fully overwrite, so no zero-fill.
+#include <torch/extension.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <c10/cuda/CUDAStream.h>
+#include <tuple>
+#include <stdexcept>
+#include "../../include/gsr.h"
+
+namespace {
+
+char* resize_cb(void* user, size_t bytes) {
+    auto* t = reinterpret_cast<torch::Tensor*>(user);
+    t->resize_({(long long)bytes});
+    return reinterpret_cast<char*>(t->data_ptr());
+}
+
+const float* fptr(const torch::Tensor& t) {      // empty tensor == "not provided" == NULL
+    return t.numel() == 0 ? nullptr : t.data_ptr<float>();
+}
+
+torch::Tensor prep(const torch::Tensor& t, const torch::Device& dev, const char* name) {
+    if (t.numel() == 0) return t;
+    TORCH_CHECK(t.scalar_type() == torch::kFloat32, name, " must be float32");
+    TORCH_CHECK(t.device() == dev, name, " must be on ", dev);
+    return t.contiguous();
+}
+
+void check(int rc) {
+    if (rc != GSR_OK) throw std::runtime_error(gsr_last_error());
+}
+
+}  // namespace
+
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+RasterizeGaussiansCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                       const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                       const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                       const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                       const int image_width, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                       const bool prefiltered, const bool debug, const int tile_row_begin, const int tile_row_end) {
+    if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const auto dev = means3D.device();
+    const int P = means3D.size(0), H = image_height, W = image_width;
+    auto fopt = means3D.options().dtype(torch::kFloat32);
+    const bool banded = !(tile_row_begin == 0 && tile_row_end == 0);
+    // the kernel writes every pixel of the rows it renders; a banded call leaves other rows at 0
+    torch::Tensor out_color = (banded || P == 0) ? torch::zeros({3, H, W}, fopt) : torch::empty({3, H, W}, fopt);
+    torch::Tensor radii = torch::empty({P}, means3D.options().dtype(torch::kInt32));
+    auto bopt = torch::TensorOptions().dtype(torch::kByte).device(dev);
+    torch::Tensor geomBuffer = torch::empty({0}, bopt), binningBuffer = torch::empty({0}, bopt), imgBuffer = torch::empty({0}, bopt);
+    int rendered = 0;
+    if (P != 0) {
+        int M = 0;
+        if (sh.numel() != 0) M = sh.size(1);
+        auto bg = prep(background, dev, "bg"), m3 = prep(means3D, dev, "means3D"), col = prep(colors, dev, "colors_precomp"),
+             op = prep(opacity, dev, "opacities"), sc = prep(scales, dev, "scales"), rot = prep(rotations, dev, "rotations"),
+             cov = prep(cov3D_precomp, dev, "cov3D_precomp"), vm = prep(viewmatrix, dev, "viewmatrix"),
+             pm = prep(projmatrix, dev, "projmatrix"), shc = prep(sh, dev, "shs"), cp = prep(campos, dev, "campos");
+        gsr_forward_args a{};
+        a.P = P; a.D = degree; a.M = M;
+        a.background = fptr(bg); a.width = W; a.height = H;
+        a.means3D = fptr(m3); a.shs = fptr(shc); a.colors_precomp = fptr(col); a.opacities = fptr(op);
+        a.scales = fptr(sc); a.scale_modifier = scale_modifier; a.rotations = fptr(rot); a.cov3D_precomp = fptr(cov);
+        a.viewmatrix = fptr(vm); a.projmatrix = fptr(pm); a.cam_pos = fptr(cp);
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = prefiltered;
+        a.out_color = out_color.data_ptr<float>(); a.radii = radii.data_ptr<int>();
+        a.debug = debug; a.tile_row_begin = tile_row_begin; a.tile_row_end = tile_row_end;
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(gsr_forward(&a, resize_cb, &geomBuffer, resize_cb, &binningBuffer, resize_cb, &imgBuffer, (void*)st, &rendered));
+    }
+    return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                               const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                               const float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                               const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                               const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
+                               const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
+                               const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
+                               const int tile_row_begin, const int tile_row_end) {
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const auto dev = means3D.device();
+    const int64_t P = means3D.size(0);
+    const int H = dL_dout_color.size(1), W = dL_dout_color.size(2);
+    int64_t M = 0;
+    if (sh.numel() != 0) M = sh.size(1);
+    auto fopt = means3D.options().dtype(torch::kFloat32);
+    // one flat gradient arena; per-Gaussian widths: mean3D 3, mean2D 3, opacity 1, sh 3M, scale 3, rot 4, colour 3, cov3D 6, conic 4
+    const int64_t widths[9] = {3, 3, 1, 3 * M, 3, 4, 3, 6, 4};
+    int64_t offs[10]; offs[0] = 0;
+    for (int i = 0; i < 9; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;   // keep 16-byte alignment
+    torch::Tensor flat = torch::empty({offs[9]}, fopt);
+    auto view = [&](int i, std::vector<int64_t> shape) { return flat.narrow(0, offs[i], widths[i] * P).view(shape); };
+    torch::Tensor dL_dmeans3D = view(0, {P, 3}), dL_dmeans2D = view(1, {P, 3}), dL_dopacity = view(2, {P, 1}),
+                  dL_dsh = view(3, {P, M, 3}), dL_dscales = view(4, {P, 3}), dL_drotations = view(5, {P, 4}),
+                  dL_dcolors = view(6, {P, 3}), dL_dcov3D = view(7, {P, 6}), dL_dconic = view(8, {P, 2, 2});
+    if (P != 0) {
+        auto bg = prep(background, dev, "bg"), m3 = prep(means3D, dev, "means3D"), col = prep(colors, dev, "colors_precomp"),
+             sc = prep(scales, dev, "scales"), rot = prep(rotations, dev, "rotations"), cov = prep(cov3D_precomp, dev, "cov3D_precomp"),
+             vm = prep(viewmatrix, dev, "viewmatrix"), pm = prep(projmatrix, dev, "projmatrix"), shc = prep(sh, dev, "shs"),
+             cp = prep(campos, dev, "campos"), dpix = prep(dL_dout_color, dev, "dL_dout_color");
+        auto rad = radii.contiguous();
+        torch::Tensor scratch = torch::empty({(int64_t)gsr_backward_scratch_bytes((int)P)}, torch::TensorOptions().dtype(torch::kByte).device(dev));
+        gsr_backward_args a{};
+        a.P = (int)P; a.D = degree; a.M = (int)M; a.R = R;
+        a.background = fptr(bg); a.width = W; a.height = H;
+        a.means3D = fptr(m3); a.shs = fptr(shc); a.colors_precomp = fptr(col); a.scales = fptr(sc);
+        a.scale_modifier = scale_modifier; a.rotations = fptr(rot); a.cov3D_precomp = fptr(cov);
+        a.viewmatrix = fptr(vm); a.projmatrix = fptr(pm); a.cam_pos = fptr(cp);
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+        a.radii = rad.data_ptr<int>();
+        a.geom_buffer = reinterpret_cast<const char*>(geomBuffer.data_ptr());
+        a.binning_buffer = reinterpret_cast<const char*>(binningBuffer.data_ptr());
+        a.image_buffer = reinterpret_cast<const char*>(imageBuffer.data_ptr());
+        a.dL_dpix = fptr(dpix);
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dconic = dL_dconic.data_ptr<float>();
+        a.dL_dopacity = dL_dopacity.data_ptr<float>(); a.dL_dcolor = dL_dcolors.data_ptr<float>();
+        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dcov3D = dL_dcov3D.data_ptr<float>();
+        a.dL_dsh = M > 0 ? dL_dsh.data_ptr<float>() : nullptr;
+        a.dL_dscale = dL_dscales.data_ptr<float>(); a.dL_drot = dL_drotations.data_ptr<float>();
+        a.grad_scratch = reinterpret_cast<float*>(scratch.data_ptr());
+        a.debug = debug; a.tile_row_begin = tile_row_begin; a.tile_row_end = tile_row_end;
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(gsr_backward(&a, (void*)st));
+    }
+    return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
+torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const int P = means3D.size(0);
+    torch::Tensor present = torch::full({P}, false, means3D.options().dtype(at::kBool));
+    if (P != 0) {
+        auto m3 = means3D.contiguous(), vm = viewmatrix.contiguous(), pm = projmatrix.contiguous();
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(means3D.device().index()).stream();
+        check(gsr_mark_visible(P, m3.data_ptr<float>(), vm.data_ptr<float>(), pm.data_ptr<float>(),
+                               reinterpret_cast<unsigned char*>(present.data_ptr<bool>()), (void*)st));
+    }
+    return present;
+}
+
+// introspection for the parity tests: (point_list, ranges, n_contrib, final_T, packed, tiles_touched, clamped) as tensors
+std::vector<torch::Tensor> viewBuffers(int P, int R, int W, int H, const torch::Tensor& geomBuffer,
+                                       const torch::Tensor& binningBuffer, const torch::Tensor& imgBuffer) {
+    gsr_buffer_view v{};
+    check(gsr_view_buffers(P, R, W, H, reinterpret_cast<const char*>(geomBuffer.data_ptr()),
+                           reinterpret_cast<const char*>(binningBuffer.data_ptr()),
+                           reinterpret_cast<const char*>(imgBuffer.data_ptr()), &v));
+    const int tiles = ((W + 15) / 16) * ((H + 15) / 16);
+    auto dev = geomBuffer.device();
+    auto mk = [&](const void* p, std::vector<int64_t> shape, torch::ScalarType dt) {
+        return torch::from_blob(const_cast<void*>(p), shape, torch::TensorOptions().dtype(dt).device(dev)).clone();
+    };
+    return {mk(v.point_list, {R}, torch::kInt32), mk(v.ranges, {tiles, 2}, torch::kInt32), mk(v.n_contrib, {H, W}, torch::kInt32),
+            mk(v.final_T, {H, W}, torch::kFloat32), mk(v.packed, {P, 12}, torch::kFloat32), mk(v.tiles_touched, {P}, torch::kInt32),
+            mk(v.clamped, {P}, torch::kUInt8)};
+}
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+    namespace py = pybind11;
+    m.def("rasterize_gaussians", &RasterizeGaussiansCUDA, py::arg("background"), py::arg("means3D"), py::arg("colors"),
+          py::arg("opacity"), py::arg("scales"), py::arg("rotations"), py::arg("scale_modifier"), py::arg("cov3D_precomp"),
+          py::arg("viewmatrix"), py::arg("projmatrix"), py::arg("tan_fovx"), py::arg("tan_fovy"), py::arg("image_height"),
+          py::arg("image_width"), py::arg("sh"), py::arg("degree"), py::arg("campos"), py::arg("prefiltered"), py::arg("debug"),
+          py::arg("tile_row_begin") = 0, py::arg("tile_row_end") = 0);
+    m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA, py::arg("background"), py::arg("means3D"),
+          py::arg("radii"), py::arg("colors"), py::arg("scales"), py::arg("rotations"), py::arg("scale_modifier"),
+          py::arg("cov3D_precomp"), py::arg("viewmatrix"), py::arg("projmatrix"), py::arg("tan_fovx"), py::arg("tan_fovy"),
+          py::arg("dL_dout_color"), py::arg("sh"), py::arg("degree"), py::arg("campos"), py::arg("geomBuffer"), py::arg("R"),
+          py::arg("binningBuffer"), py::arg("imageBuffer"), py::arg("debug"), py::arg("tile_row_begin") = 0,
+          py::arg("tile_row_end") = 0);
+    m.def("mark_visible", &markVisible);
+    m.def("view_buffers", &viewBuffers);
+}
