@@ -9,8 +9,51 @@
 #include "gsr_internal.cuh"
 #include <string>
 #include <cstdio>
+#include <atomic>
 
 using namespace gsr;
+
+// ---- launch counter + optional per-stage CUDA-event timing (bench.py's roofline leg) -----------
+static std::atomic<unsigned long long> g_launches{0};
+namespace gsr { void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); } }
+
+enum Stage { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SORT, ST_RANGES, ST_RENDER,
+             ST_BWD_ZERO, ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT };
+static const char* const k_stage_names[ST_COUNT] = {"preprocess", "depth_sort", "scan", "duplicate", "tile_sort", "tile_ranges",
+                                                    "render", "bwd_zero", "render_bwd", "preprocess_bwd"};
+static int g_profiling = 0;
+static cudaEvent_t g_ev[ST_COUNT][2];
+static bool g_ev_made = false, g_ev_pending[ST_COUNT];
+static double g_stage_sum_ms[ST_COUNT];
+static int g_stage_n[ST_COUNT], g_stage_dropped[ST_COUNT];
+
+// Fold a finished (start, stop) pair of stage s into its running mean.  Never blocks unless `wait`.
+static void harvest_stage(int s, bool wait) {
+    if (!g_ev_made || !g_ev_pending[s]) return;
+    cudaError_t q = wait ? cudaEventSynchronize(g_ev[s][1]) : cudaEventQuery(g_ev[s][1]);
+    if (q == cudaSuccess) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, g_ev[s][0], g_ev[s][1]) == cudaSuccess) { g_stage_sum_ms[s] += ms; g_stage_n[s]++; }
+    } else {
+        if (q == cudaErrorNotReady) (void)cudaGetLastError();
+        g_stage_dropped[s]++;
+    }
+    g_ev_pending[s] = false;
+}
+
+struct StageTimer {        // records start/stop events around one stage on the launching stream
+    int s; cudaStream_t st; bool on;
+    StageTimer(int stage, cudaStream_t stream) : s(stage), st(stream), on(g_profiling != 0) {
+        if (!on) return;
+        if (!g_ev_made) {
+            for (int i = 0; i < ST_COUNT; i++) { cudaEventCreate(&g_ev[i][0]); cudaEventCreate(&g_ev[i][1]); g_ev_pending[i] = false; }
+            g_ev_made = true;
+        }
+        harvest_stage(s, false);     // the previous step's pair for this stage has long finished (the forward syncs once)
+        cudaEventRecord(g_ev[s][0], st);
+    }
+    ~StageTimer() { if (on) { cudaEventRecord(g_ev[s][1], st); g_ev_pending[s] = true; } }
+};
 
 static thread_local std::string g_err;
 static thread_local uint32_t* g_pinned = nullptr;
@@ -43,6 +86,23 @@ extern "C" {
 
 const char* gsr_last_error(void) { return g_err.c_str(); }
 int gsr_version(void) { return GSR_VERSION; }
+
+unsigned long long gsr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+void gsr_set_profiling(int on) {
+    g_profiling = on;
+    if (on) for (int i = 0; i < ST_COUNT; i++) { g_stage_sum_ms[i] = 0.0; g_stage_n[i] = 0; g_stage_dropped[i] = 0; }
+}
+int gsr_num_stages(void) { return ST_COUNT; }
+const char* gsr_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? k_stage_names[i] : ""; }
+int gsr_get_stage_ms(float* mean_ms, int* samples, int n) {
+    if (!mean_ms || n < ST_COUNT) return fail(GSR_ERR_INVALID_ARGUMENT, "need room for gsr_num_stages() entries");
+    for (int i = 0; i < ST_COUNT; i++) {
+        harvest_stage(i, true);
+        mean_ms[i] = g_stage_n[i] ? (float)(g_stage_sum_ms[i] / g_stage_n[i]) : -1.0f;
+        if (samples) samples[i] = g_stage_n[i];
+    }
+    return GSR_OK;
+}
 
 size_t gsr_backward_scratch_bytes(int P) { return (size_t)(P > 0 ? P : 0) * 12 * sizeof(float) + 256; }
 
@@ -110,17 +170,23 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     pa.prefiltered = a->prefiltered;
     pa.radii = radii; pa.packed = geom.packed; pa.tiles_touched = geom.tiles_touched; pa.clamped = geom.clamped;
     pa.depth_keys = geom.keys[0]; pa.ids = geom.vals[0];
-    launch_preprocess(pa, st);
+    { StageTimer t(ST_PREPROCESS, st); launch_preprocess(pa, st); }
     GSR_STAGE("preprocess", st, a->debug);
 
     // depth order of the Gaussians: 4 stable 8-bit passes, result back in keys[0]/vals[0]
-    for (int pass = 0; pass < 4; pass++) {
-        const int s = pass & 1;
-        radix_pass_u32(geom.keys[s], geom.vals[s], geom.keys[s ^ 1], geom.vals[s ^ 1], P, 8 * pass, 8, geom.table, geom.scan_tmp, st);
+    {
+        StageTimer t(ST_DEPTH_SORT, st);
+        for (int pass = 0; pass < 4; pass++) {
+            const int s = pass & 1;
+            radix_pass_u32(geom.keys[s], geom.vals[s], geom.keys[s ^ 1], geom.vals[s ^ 1], P, 8 * pass, 8, geom.table, geom.scan_tmp, st);
+        }
     }
     GSR_STAGE("depth sort", st, a->debug);
-    launch_gather_u32(geom.tiles_touched, geom.vals[0], geom.tt_sorted, P, st);
-    scan_exclusive_u32(geom.tt_sorted, geom.offsets, P, geom.scan_tmp, geom.total, st);
+    {
+        StageTimer t(ST_SCAN, st);
+        launch_gather_u32(geom.tiles_touched, geom.vals[0], geom.tt_sorted, P, st);
+        scan_exclusive_u32(geom.tt_sorted, geom.offsets, P, geom.scan_tmp, geom.total, st);
+    }
     GSR_STAGE("scan", st, a->debug);
 
     if (!g_pinned) GSR_CUDA(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
@@ -136,19 +202,28 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     const int tile_bits = bits_for((uint32_t)tiles);
     const int npass = (tile_bits + 7) / 8;
     int s = npass & 1;       // start so that the last pass lands in vals[0] == point_list
-    launch_duplicate(P, geom.vals[0], geom.offsets, geom.tt_sorted, geom.packed, radii, grid_x, grid_y, row_begin, row_end,
-                     bin.keys[s], bin.vals[s], st);
+    {
+        StageTimer t(ST_DUPLICATE, st);
+        launch_duplicate(P, geom.vals[0], geom.offsets, geom.tt_sorted, geom.packed, radii, grid_x, grid_y, row_begin, row_end,
+                         bin.keys[s], bin.vals[s], st);
+    }
     GSR_STAGE("duplicate", st, a->debug);
-    for (int pass = 0; pass < npass; pass++) {
-        const int bits = (tile_bits - 8 * pass) < 8 ? (tile_bits - 8 * pass) : 8;
-        radix_pass_u32(bin.keys[s], bin.vals[s], bin.keys[s ^ 1], bin.vals[s ^ 1], R, 8 * pass, bits, bin.table, bin.scan_tmp, st);
-        s ^= 1;
+    {
+        StageTimer t(ST_TILE_SORT, st);
+        for (int pass = 0; pass < npass; pass++) {
+            const int bits = (tile_bits - 8 * pass) < 8 ? (tile_bits - 8 * pass) : 8;
+            radix_pass_u32(bin.keys[s], bin.vals[s], bin.keys[s ^ 1], bin.vals[s ^ 1], R, 8 * pass, bits, bin.table, bin.scan_tmp, st);
+            s ^= 1;
+        }
     }
     GSR_STAGE("tile sort", st, a->debug);
-    launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st);
+    { StageTimer t(ST_RANGES, st); launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st); }
     GSR_STAGE("tile ranges", st, a->debug);
-    launch_render_forward(grid_x, row_begin, row_end, img.ranges, bin.vals[0], W, H, geom.packed, a->background,
-                          a->out_color, img.final_T, img.n_contrib, st);
+    {
+        StageTimer t(ST_RENDER, st);
+        launch_render_forward(grid_x, row_begin, row_end, img.ranges, bin.vals[0], W, H, geom.packed, a->background,
+                              a->out_color, img.final_T, img.n_contrib, st);
+    }
     GSR_STAGE("render", st, a->debug);
     *num_rendered = (int)R;
     return GSR_OK;
@@ -176,10 +251,15 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     ImageState img = ImageState::carve((char*)align_up((size_t)a->image_buffer, 256), (size_t)W * H, tiles);
 
     float* acc = (float*)align_up((size_t)a->grad_scratch, 256);
-    GSR_CUDA(cudaMemsetAsync(acc, 0, (size_t)P * 12 * sizeof(float), st));
-    if (a->R > 0)
+    {
+        StageTimer t(ST_BWD_ZERO, st);
+        GSR_CUDA(cudaMemsetAsync(acc, 0, (size_t)P * 12 * sizeof(float), st));
+    }
+    if (a->R > 0) {
+        StageTimer t(ST_RENDER_BWD, st);
         launch_render_backward(grid_x, row_begin, row_end, img.ranges, bin.vals[0], W, H, geom.packed, a->background,
                                img.final_T, img.n_contrib, a->dL_dpix, acc, st);
+    }
     GSR_STAGE("render backward", st, a->debug);
 
     PreprocessBwdArgs pb;
@@ -193,7 +273,7 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     pb.grad_acc = acc;
     pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dconic = a->dL_dconic; pb.dL_dopacity = a->dL_dopacity; pb.dL_dcolor = a->dL_dcolor;
     pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh; pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
-    launch_preprocess_backward(pb, st);
+    { StageTimer t(ST_PREPROCESS_BWD, st); launch_preprocess_backward(pb, st); }
     GSR_STAGE("preprocess backward", st, a->debug);
     return GSR_OK;
 }

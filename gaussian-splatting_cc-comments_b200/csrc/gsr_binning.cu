@@ -133,6 +133,7 @@ void scan_exclusive_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t* t
     scan_block_sums_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, n, tmp);
     scan_sums_kernel<<<1, 1024, 0, st>>>(tmp, nb, total);
     scan_apply_kernel<<<(unsigned)nb, SCAN_THREADS, 0, st>>>(in, out, n, tmp);
+    count_launch(3);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -222,6 +223,7 @@ void radix_pass_u32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, ui
     rs_hist_kernel<<<nb, RS_THREADS, 0, st>>>(kin, n, shift, bits, table, nb);
     scan_exclusive_u32(table, table, tbl, scan_tmp, nullptr, st);
     rs_scatter_kernel<<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, table, nb);
+    count_launch(2);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -233,6 +235,7 @@ __global__ void __launch_bounds__(256) gather_u32_kernel(const uint32_t* __restr
 void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, size_t n, cudaStream_t st) {
     if (n == 0) return;
     gather_u32_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(src, idx, dst, n);
+    count_launch(1);
 }
 
 // duplicateWithKeys (rasterizer_impl.cu:78-126), walked in depth order; key = tile id only.
@@ -264,6 +267,7 @@ void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, con
     if (P <= 0) return;
     duplicate_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
                                                       row_begin, row_end, tile_keys, vals);
+    count_launch(1);
 }
 
 // identifyTileRanges (rasterizer_impl.cu:133-159); ranges are zeroed first (:377)
@@ -286,6 +290,7 @@ void launch_tile_ranges(size_t R, const uint32_t* sorted_tile_keys, uint2* range
     cudaMemsetAsync(ranges, 0, tiles * sizeof(uint2), st);
     if (R == 0) return;
     tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, sorted_tile_keys, ranges);
+    count_launch(1);
 }
 
 }  // namespace gsr

@@ -113,6 +113,8 @@ struct ImageState {
     }
 };
 
+void count_launch(int n);   // bumps the library-wide kernel launch counter (gsr_launch_count)
+
 // ---- stage launchers (each enqueues on `st`, none synchronises) --------------------------------
 struct Camera {             // device pointers, read once per block
     const float* view; const float* proj; const float* campos;

@@ -172,6 +172,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
     preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    count_launch(1);
 }
 
 // rasterizer_impl.cu:56-69 (checkFrustum) -> present[idx] = p_view.z > 0.2 (auxiliary.h:165)
@@ -188,6 +189,7 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
 void launch_mark_visible(int P, const float* means, const float* view, unsigned char* present, cudaStream_t st) {
     if (P <= 0) return;
     mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means, view, present);
+    count_launch(1);
 }
 
 }  // namespace gsr

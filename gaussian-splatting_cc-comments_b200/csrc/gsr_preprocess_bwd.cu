@@ -219,6 +219,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel(PreprocessBwdArgs a
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
     preprocess_bwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    count_launch(1);
 }
 
 }  // namespace gsr

@@ -179,6 +179,7 @@ void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2*
     dim3 grid(grid_x, row_end - row_begin, 1);
     render_bwd_kernel<<<grid, 256, 0, st>>>(ranges, point_list, W, H, grid_x, row_begin, packed, bg, final_T, n_contrib,
                                              dL_dpix, grad_acc);
+    count_launch(1);
 }
 
 }  // namespace gsr

@@ -1,0 +1,193 @@
+"""One-process-per-GPU partitioning of the rasterizer over a single NVSwitch box.
+
+Two workloads shard naturally; nothing else is distributed:
+
+* render-only: the image's TILE ROWS are split across ranks, Gaussians and camera replicated.
+  Each rank runs the full per-Gaussian stage (radii are identical everywhere), bins and blends
+  only the instances that fall in its band (`tile_row_begin/end` of the C ABI, include/gsr.h) and
+  the bands are exchanged with one all-gather.  No per-Gaussian collective.
+* multi-view training: one camera per rank, parameters replicated; each rank's per-Gaussian
+  gradients are summed with ONE all-reduce over the flat gradient arena the backward writes
+  (the torch binding returns all gradients as views of one buffer), `radii` with a max-reduce.
+
+The collective backend is whatever `torch.distributed` was initialised with: NCCL over
+NVLink 5 / NVSwitch on the B200 box, gloo in the CPU tests of the host-side logic.
+The reference has no multi-GPU path (train.py is single-device); this is an extension around the
+drop-in API and does not change it.
+"""
+from typing import List, NamedTuple, Optional, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+TILE = 16   # DGR config.h:16-17 (BLOCK_X, BLOCK_Y)
+
+
+class BandedRasterizationSettings(NamedTuple):
+    """GaussianRasterizationSettings (DGR/diff_gaussian_rasterization/__init__.py:168-180) plus the
+    tile-row band this rank renders."""
+    image_height: int
+    image_width: int
+    tanfovx: float
+    tanfovy: float
+    bg: torch.Tensor
+    scale_modifier: float
+    viewmatrix: torch.Tensor
+    projmatrix: torch.Tensor
+    sh_degree: int
+    campos: torch.Tensor
+    prefiltered: bool
+    debug: bool
+    tile_rows: Tuple[int, int] = (0, 0)
+
+
+def tile_rows(image_height: int) -> int:
+    return (image_height + TILE - 1) // TILE
+
+
+def split_tile_rows(n_rows: int, world: int, row_weights: Optional[Sequence[float]] = None) -> List[Tuple[int, int]]:
+    """Contiguous bands [begin, end) of tile rows, one per rank, covering [0, n_rows) exactly once.
+
+    Without weights rows are split as evenly as possible (earlier ranks take the remainder).  With
+    `row_weights` (e.g. instances per tile row from a previous frame) the cut points are the weighted
+    quantiles, so every rank blends about the same number of instances.  A rank may get an empty band
+    when world > n_rows.
+    """
+    if world <= 0:
+        raise ValueError("world must be positive")
+    if n_rows < 0:
+        raise ValueError("n_rows must be non-negative")
+    if row_weights is None:
+        base, rem = divmod(n_rows, world)
+        bands, b = [], 0
+        for r in range(world):
+            e = b + base + (1 if r < rem else 0)
+            bands.append((b, e))
+            b = e
+        return bands
+    w = [max(float(x), 0.0) for x in row_weights]
+    if len(w) != n_rows:
+        raise ValueError("row_weights must have one entry per tile row")
+    total = sum(w)
+    if total <= 0.0:
+        return split_tile_rows(n_rows, world)
+    cuts, acc, row = [0], 0.0, 0
+    for r in range(1, world):
+        target = total * r / world
+        while row < n_rows and acc + 0.5 * w[row] < target:
+            acc += w[row]
+            row += 1
+        cuts.append(row)
+    cuts.append(n_rows)
+    return [(cuts[i], cuts[i + 1]) for i in range(world)]
+
+
+def band_pixel_rows(band: Tuple[int, int], image_height: int) -> Tuple[int, int]:
+    return min(band[0] * TILE, image_height), min(band[1] * TILE, image_height)
+
+
+def banded_settings(settings, band: Tuple[int, int]) -> BandedRasterizationSettings:
+    return BandedRasterizationSettings(*tuple(settings)[:12], tile_rows=(int(band[0]), int(band[1])))
+
+
+def gather_bands(local_rows: torch.Tensor, bands: Sequence[Tuple[int, int]], image_height: int,
+                 group=None) -> torch.Tensor:
+    """All-gather the per-rank (3, rows_r, W) bands into the full (3, H, W) image on every rank.
+
+    Bands differ in height, so each rank pads to the tallest band; the exchange is a single
+    all_gather_into_tensor (99.5 MB at 4K in total)."""
+    world = dist.get_world_size(group)
+    heights = [band_pixel_rows(b, image_height) for b in bands]
+    hmax = max(e - b for b, e in heights)
+    C, _, W = local_rows.shape
+    send = local_rows.new_zeros((C, hmax, W))
+    send[:, : local_rows.shape[1]] = local_rows
+    recv = local_rows.new_empty((world, C, hmax, W))
+    dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
+    out = local_rows.new_empty((C, image_height, W))
+    for r, (b, e) in enumerate(heights):
+        out[:, b:e] = recv[r, :, : e - b]
+    return out
+
+
+def render_tile_row_sharded(rasterizer_cls, settings, *, means3D, means2D, opacities, shs=None, colors_precomp=None,
+                            scales=None, rotations=None, cov3D_precomp=None, row_weights=None, group=None,
+                            gather=True):
+    """Render-only forward with the image's tile rows split over the ranks of `group`.
+
+    Returns (image, radii, band).  `image` is the full (3,H,W) frame when gather=True, else this
+    rank's (3, rows, W) band.  radii are computed on the full image on every rank."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    H = int(settings.image_height)
+    bands = split_tile_rows(tile_rows(H), world, row_weights)
+    band = bands[rank]
+    with torch.no_grad():
+        if band[1] > band[0]:
+            rast = rasterizer_cls(raster_settings=banded_settings(settings, band))
+            color, radii = rast(means3D=means3D, means2D=means2D, opacities=opacities, shs=shs,
+                                colors_precomp=colors_precomp, scales=scales, rotations=rotations,
+                                cov3D_precomp=cov3D_precomp)
+        else:   # more ranks than tile rows: this rank only contributes radii
+            rast = rasterizer_cls(raster_settings=banded_settings(settings, (0, 1)))
+            color, radii = rast(means3D=means3D, means2D=means2D, opacities=opacities, shs=shs,
+                                colors_precomp=colors_precomp, scales=scales, rotations=rotations,
+                                cov3D_precomp=cov3D_precomp)
+        p0, p1 = band_pixel_rows(band, H)
+        local = color[:, p0:p1]
+        if not gather or world == 1:
+            return (color if world == 1 else local), radii, band
+        return gather_bands(local.contiguous(), bands, H, group), radii, band
+
+
+def flat_span(tensors: Sequence[torch.Tensor]) -> Optional[torch.Tensor]:
+    """If every tensor is a dense view into ONE storage (the backward's gradient arena), return the 1-D
+    tensor that covers them all, else None."""
+    ts = [t for t in tensors if t is not None and t.numel() > 0]
+    if not ts:
+        return None
+    st = ts[0].untyped_storage()
+    lo, hi = None, None
+    for t in ts:
+        if t.untyped_storage().data_ptr() != st.data_ptr() or not t.is_contiguous() or t.dtype != ts[0].dtype:
+            return None
+        b = t.storage_offset()
+        e = b + t.numel()
+        lo = b if lo is None else min(lo, b)
+        hi = e if hi is None else max(hi, e)
+    return torch.empty(0, dtype=ts[0].dtype, device=ts[0].device).set_(st, lo, (hi - lo,), (1,))
+
+
+def allreduce_gradients(grads: Sequence[torch.Tensor], group=None, average=False) -> int:
+    """Sum per-Gaussian gradients over the ranks (one camera each).  One collective when the gradients
+    share the backward's flat arena, else one per tensor.  Returns the number of collectives issued."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return 0
+    world = dist.get_world_size(group)
+    flat = flat_span(grads)
+    n = 0
+    if flat is not None:
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        if average:
+            flat.div_(world)
+        return 1
+    for g in grads:
+        if g is None or g.numel() == 0:
+            continue
+        dist.all_reduce(g, op=dist.ReduceOp.SUM, group=group)
+        if average:
+            g.div_(world)
+        n += 1
+    return n
+
+
+def allreduce_radii(radii: torch.Tensor, group=None) -> torch.Tensor:
+    """max_radii2D needs the elementwise max over views (train.py:157)."""
+    if dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(radii, op=dist.ReduceOp.MAX, group=group)
+    return radii
+
+
+def cameras_for_rank(n_views: int, rank: int, world: int) -> List[int]:
+    """View c goes to rank c mod world: 8/4/2/1 views per GPU per step at 1/2/4/8 GPUs."""
+    return [c for c in range(n_views) if c % world == rank]

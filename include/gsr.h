@@ -145,6 +145,18 @@ int gsr_view_buffers(int P, int R, int width, int height, const char* geom_buffe
 const char* gsr_last_error(void);
 int gsr_version(void);
 
+/* Measurement hooks (bench.py): number of kernels this library has launched since load, and optional
+ * per-stage timing.  With profiling on, CUDA events are recorded on the launching stream around each stage
+ * of gsr_forward / gsr_backward (preprocess, depth_sort, scan, duplicate, tile_sort, tile_ranges, render,
+ * bwd_zero, render_bwd, preprocess_bwd) and folded into a running mean per stage without blocking.
+ * gsr_set_profiling(1) clears the means; gsr_get_stage_ms waits for the last events and returns the mean
+ * milliseconds (-1 = never ran) and sample counts.  Off by default (no events recorded). */
+unsigned long long gsr_launch_count(void);
+void gsr_set_profiling(int on);
+int gsr_num_stages(void);
+const char* gsr_stage_name(int i);
+int gsr_get_stage_ms(float* mean_ms, int* samples, int n);
+
 #ifdef __cplusplus
 }
 #endif

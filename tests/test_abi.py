@@ -1,0 +1,140 @@
+"""C-ABI library: loads without a GPU, exports every symbol include/gsr.h declares, and its host-side
+logic (sizes, argument validation, error text) behaves.  No compute calls here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+LIB = os.path.join(ROOT, "gaussian-splatting_cc-comments_b200", "libgsr_b200.so")
+HDR = os.path.join(ROOT, "include", "gsr.h")
+
+
+def declared_functions():
+    src = open(HDR).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    names = re.findall(r"\b(gsr_[a-z0-9_]+)\s*\(", src)
+    typedef_fn = set(re.findall(r"\(\*\s*(gsr_[a-z0-9_]+)\s*\)", src))
+    return sorted(set(names) - typedef_fn)
+
+
+@pytest.fixture(scope="module")
+def lib():
+    return C.CDLL(LIB)
+
+
+def test_header_declares_the_path():
+    fns = declared_functions()
+    for must in ("gsr_forward", "gsr_backward", "gsr_mark_visible", "gsr_required_bytes", "gsr_last_error"):
+        assert must in fns
+
+
+def test_every_declared_symbol_is_exported(lib):
+    for name in declared_functions():
+        assert hasattr(lib, name), "libgsr_b200.so does not export " + name
+
+
+def test_version(lib):
+    assert lib.gsr_version() == 1
+
+
+def test_required_bytes_monotone_and_aligned(lib):
+    lib.gsr_required_bytes.restype = C.c_size_t
+    lib.gsr_required_bytes.argtypes = [C.c_int, C.c_size_t, C.c_size_t]
+    prev = 0
+    for n in (0, 1, 1000, 10**6, 3 * 10**6):
+        b = lib.gsr_required_bytes(0, n, 0)
+        assert b >= prev and b % 256 == 0
+        prev = b
+    # geometry state: 48 B record + sort/scan arrays; stays well under the reference's 79 B + CUB temp x2
+    per = lib.gsr_required_bytes(0, 3 * 10**6, 0) / 3e6
+    assert 48 <= per <= 100
+    per_inst = lib.gsr_required_bytes(1, 12 * 10**6, 0) / 12e6
+    assert 16 <= per_inst <= 20                      # 2 x (tile key + id) ping-pong = 16 B / instance
+    img = lib.gsr_required_bytes(2, 1920 * 1080, 120 * 68)
+    assert img >= 1920 * 1080 * 8 + 120 * 68 * 8
+    assert lib.gsr_required_bytes(7, 10, 0) == 0
+
+
+def test_scratch_bytes(lib):
+    lib.gsr_backward_scratch_bytes.restype = C.c_size_t
+    assert lib.gsr_backward_scratch_bytes(0) >= 0
+    assert lib.gsr_backward_scratch_bytes(1000) >= 1000 * 48
+
+
+def test_stage_names(lib):
+    lib.gsr_stage_name.restype = C.c_char_p
+    n = lib.gsr_num_stages()
+    names = [lib.gsr_stage_name(i).decode() for i in range(n)]
+    assert names[0] == "preprocess" and "render" in names and "render_bwd" in names and "preprocess_bwd" in names
+    assert lib.gsr_stage_name(99) == b""
+
+
+class FwdArgs(C.Structure):
+    _fields_ = [("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("background", C.c_void_p), ("width", C.c_int),
+                ("height", C.c_int), ("means3D", C.c_void_p), ("shs", C.c_void_p), ("colors_precomp", C.c_void_p),
+                ("opacities", C.c_void_p), ("scales", C.c_void_p), ("scale_modifier", C.c_float),
+                ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p),
+                ("projmatrix", C.c_void_p), ("cam_pos", C.c_void_p), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
+                ("prefiltered", C.c_int), ("out_color", C.c_void_p), ("radii", C.c_void_p), ("debug", C.c_int),
+                ("tile_row_begin", C.c_int), ("tile_row_end", C.c_int)]
+
+
+RESIZE = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+
+
+def _call_forward(lib, args):
+    cb = RESIZE(lambda user, n: None)
+    nr = C.c_int(-5)
+    lib.gsr_last_error.restype = C.c_char_p
+    rc = lib.gsr_forward(C.byref(args), cb, None, cb, None, cb, None, None, C.byref(nr))
+    return rc, nr.value, lib.gsr_last_error().decode()
+
+
+def test_forward_rejects_bad_arguments_without_touching_the_gpu(lib):
+    a = FwdArgs()
+    a.P, a.width, a.height = -1, 16, 16
+    rc, nr, msg = _call_forward(lib, a)
+    assert rc == 1 and "bad sizes" in msg and nr == 0
+    a.P, a.width = 10, 0
+    rc, _, _ = _call_forward(lib, a)
+    assert rc == 1
+    a.width = 16
+    rc, _, msg = _call_forward(lib, a)           # required pointers missing
+    assert rc == 1 and "pointer" in msg
+    rc = lib.gsr_forward(None, None, None, None, None, None, None, None, None)
+    assert rc == 1
+
+
+def test_forward_with_no_gaussians_is_a_no_op(lib):
+    """P == 0 returns before any launch (rasterize_points.cu:94)."""
+    a = FwdArgs()
+    a.P, a.width, a.height = 0, 32, 32
+    rc, nr, _ = _call_forward(lib, a)
+    assert rc == 0 and nr == 0
+
+
+def test_mark_visible_argument_checks(lib):
+    assert lib.gsr_mark_visible(0, None, None, None, None, None) == 0
+    assert lib.gsr_mark_visible(-1, None, None, None, None, None) == 1
+    assert lib.gsr_mark_visible(5, None, None, None, None, None) == 1
+
+
+def test_backward_argument_checks(lib):
+    assert lib.gsr_backward(None, None) == 1
+
+
+def test_launch_counter_starts_at_zero_on_cpu(lib):
+    lib.gsr_launch_count.restype = C.c_ulonglong
+    assert lib.gsr_launch_count() == 0
+
+
+def test_library_has_no_cpu_fallback_symbols():
+    """The product library must not link the oracle."""
+    import subprocess
+    out = subprocess.run(["nm", "-D", LIB], capture_output=True, text=True).stdout
+    assert "gso_" not in out
+    ext = os.path.join(ROOT, "gaussian-splatting_cc-comments_b200", "diff_gaussian_rasterization", "_C.so")
+    out = subprocess.run(["nm", "-D", ext], capture_output=True, text=True).stdout
+    assert "gso_" not in out
