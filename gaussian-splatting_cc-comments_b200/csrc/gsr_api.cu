@@ -210,9 +210,12 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     GSR_STAGE("duplicate", st, a->debug);
     {
         StageTimer t(ST_TILE_SORT, st);
-        for (int pass = 0; pass < npass; pass++) {
-            const int bits = (tile_bits - 8 * pass) < 8 ? (tile_bits - 8 * pass) : 8;
-            radix_pass_u32(bin.keys[s], bin.vals[s], bin.keys[s ^ 1], bin.vals[s ^ 1], R, 8 * pass, bits, bin.table, bin.scan_tmp, st);
+        // digits of equal width (13 tile bits -> 7 + 6): fewer bins per pass = longer contiguous runs per block
+        const int per = npass ? (tile_bits + npass - 1) / npass : 0;
+        for (int pass = 0, shift = 0; pass < npass; pass++) {
+            const int bits = (tile_bits - shift) < per ? (tile_bits - shift) : per;
+            radix_pass_u32(bin.keys[s], bin.vals[s], bin.keys[s ^ 1], bin.vals[s ^ 1], R, shift, bits, bin.table, bin.scan_tmp, st);
+            shift += bits;
             s ^= 1;
         }
     }

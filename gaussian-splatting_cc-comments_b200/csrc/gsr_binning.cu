@@ -139,90 +139,166 @@ void scan_exclusive_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t* t
 // ------------------------------------------------------------------------------------------------
 // stable LSD radix sort pass on (u32 key, u32 value) pairs, <= 8 key bits per pass
 // ------------------------------------------------------------------------------------------------
-// Each block owns RS_TILE consecutive items; warp w owns the w-th 512-item slice and walks it in
-// 16 rounds of 32 consecutive items, so "earlier in the input" == (lower warp, lower round, lower
-// lane).  Within a round lanes with equal digits find each other with match.any; the lowest such
-// lane bumps the warp's private digit counter.  No atomics, fully deterministic.
-__device__ __forceinline__ void rs_rank_tile(const uint32_t* __restrict__ keys, size_t n, size_t tile_base, int shift, uint32_t mask,
-                                             uint32_t* s_hist /* [8][RS_BINS] */, uint32_t* key_out, uint32_t* rank_out) {
+// One pass = a histogram kernel (global digit counts) + ONE single-sweep kernel: each block takes a ticket
+// (blocks therefore start in tile order), ranks its 4096 items, publishes its per-digit counts and obtains
+// the counts of all earlier tiles with a decoupled look-back over a status-tagged table, reorders its
+// items by digit in shared memory and writes them out as contiguous runs.  Per item the pass moves
+// 4 B (histogram read) + 8 B read + 8 B write.  Deterministic and stable: a tile's items keep their input
+// order within each digit, tiles are concatenated in order.
+//
+// Ranking: warp w owns the w-th 512-item slice of the tile and walks it in 16 rounds of 32 consecutive
+// items, so "earlier in the input" == (lower warp, lower round, lower lane).  Within a round lanes with
+// equal digits find each other with match.any; the lowest such lane bumps the warp's private digit counter.
+constexpr uint32_t LB_AGG = 1u << 30, LB_PREFIX = 2u << 30, LB_MASK = (1u << 30) - 1u;
+
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, int shift, int bits,
+                                                             uint32_t* __restrict__ ghist) {
+    __shared__ uint32_t s_hist[8 * RS_BINS];
+    const uint32_t mask = (1u << bits) - 1u;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     uint32_t* wh = s_hist + w * RS_BINS;
     for (int i = lane; i < RS_BINS; i += 32) wh[i] = 0;
     __syncwarp();
-    const uint32_t lt = (1u << lane) - 1u;
-    const size_t wbase = tile_base + (size_t)w * (32 * RS_ITEMS);
+    const size_t n4 = n >> 2;
+    const uint4* k4 = reinterpret_cast<const uint4*>(keys);
+    // warp-uniform trip count (the loop body votes): lanes past the end carry an impossible digit
+    for (size_t base = (size_t)blockIdx.x * RS_THREADS + (size_t)w * 32; base < n4; base += (size_t)gridDim.x * RS_THREADS) {
+        const size_t i = base + lane;
+        const bool ok = i < n4;
+        const uint4 q = ok ? __ldg(k4 + i) : make_uint4(0, 0, 0, 0);
+        const uint32_t d[4] = {(q.x >> shift) & mask, (q.y >> shift) & mask, (q.z >> shift) & mask, (q.w >> shift) & mask};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            // whole warp on one digit (high bytes of depth keys): one add instead of a 32-way same-address atomic
+            const uint32_t dj = ok ? d[j] : 0xFFFFFFFFu;
+            const uint32_t d0 = __shfl_sync(0xffffffffu, dj, 0);
+            if (__all_sync(0xffffffffu, dj == d0)) { if (lane == 0) wh[d0] += 32; }
+            else if (ok) atomicAdd(&wh[dj], 1u);
+            __syncwarp();
+        }
+    }
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) atomicAdd(&wh[(keys[4 * n4 + threadIdx.x] >> shift) & mask], 1u);
+    __syncthreads();
+    const int d = threadIdx.x;   // RS_THREADS == RS_BINS
+    uint32_t c = 0;
+#pragma unroll
+    for (int ww = 0; ww < 8; ww++) c += s_hist[ww * RS_BINS + d];
+    if (c) atomicAdd(&ghist[d], c);
+}
+
+__global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
+                                                              uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, size_t n,
+                                                              int shift, int bits, const uint32_t* __restrict__ ghist,
+                                                              uint32_t* ticket, uint32_t* lookback) {
+    __shared__ uint32_t s_hist[8 * RS_BINS];
+    __shared__ uint32_t s_keys[RS_TILE];
+    __shared__ uint32_t s_vals[RS_TILE];
+    __shared__ uint32_t s_dstart[RS_BINS];     // first local (digit-sorted) position of each digit
+    __shared__ uint32_t s_gbase[RS_BINS];      // global position of local position 0 of each digit's run
+    __shared__ uint32_t s_warp[RS_THREADS / 32 + 1];
+    __shared__ uint32_t s_bid;
+    if (threadIdx.x == 0) s_bid = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const uint32_t bid = s_bid;
+    const uint32_t mask = (1u << bits) - 1u;
+    const int radix = 1 << bits;
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const size_t tile_base = (size_t)bid * RS_TILE;
+    const int tile_n = (int)min((size_t)RS_TILE, n - tile_base);
+
+    // ---- rank ----
+    uint32_t* wh = s_hist + w * RS_BINS;
+    for (int i = lane; i < RS_BINS; i += 32) wh[i] = 0;
+    const int wofs = w * (32 * RS_ITEMS);
+    uint32_t key[RS_ITEMS];
+    uint16_t rank[RS_ITEMS];
 #pragma unroll
     for (int r = 0; r < RS_ITEMS; r++) {
-        const size_t i = wbase + (size_t)r * 32 + lane;
-        const bool valid = i < n;
-        const uint32_t key = valid ? keys[i] : 0u;
-        const uint32_t d = valid ? ((key >> shift) & mask) : 0xFFFFFFFFu;
+        const int li = wofs + r * 32 + lane;
+        key[r] = (li < tile_n) ? kin[tile_base + li] : 0xFFFFFFFFu;
+    }
+    __syncwarp();
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int r = 0; r < RS_ITEMS; r++) {
+        const bool valid = wofs + r * 32 + lane < tile_n;
+        const uint32_t d = valid ? ((key[r] >> shift) & mask) : 0xFFFFFFFFu;
         const uint32_t peers = __match_any_sync(0xffffffffu, d);
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
         if (valid && lane == leader) { old = wh[d]; wh[d] = old + __popc(peers); }
         old = __shfl_sync(0xffffffffu, old, leader);
-        __syncwarp();
-        if (key_out) { key_out[r] = key; rank_out[r] = old + __popc(peers & lt); }
+        rank[r] = (uint16_t)(old + __popc(peers & lt));
     }
-}
-
-__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, int shift, int bits,
-                                                             uint32_t* __restrict__ table, unsigned nblocks) {
-    __shared__ uint32_t s_hist[8 * RS_BINS];
-    const uint32_t mask = (1u << bits) - 1u;
-    rs_rank_tile(keys, n, (size_t)blockIdx.x * RS_TILE, shift, mask, s_hist, nullptr, nullptr);
     __syncthreads();
-    const int d = threadIdx.x;   // RS_THREADS == RS_BINS
-    uint32_t c = 0;
-#pragma unroll
-    for (int w = 0; w < 8; w++) c += s_hist[w * RS_BINS + d];
-    if (d < (1 << bits)) table[(size_t)d * nblocks + blockIdx.x] = c;
-}
 
-__global__ void __launch_bounds__(RS_THREADS) rs_scatter_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
-                                                                uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, size_t n,
-                                                                int shift, int bits, const uint32_t* __restrict__ table, unsigned nblocks) {
-    __shared__ uint32_t s_hist[8 * RS_BINS];
-    const uint32_t mask = (1u << bits) - 1u;
-    uint32_t key[RS_ITEMS], rank[RS_ITEMS];
-    const size_t tile_base = (size_t)blockIdx.x * RS_TILE;
-    rs_rank_tile(kin, n, tile_base, shift, mask, s_hist, key, rank);
-    __syncthreads();
-    {   // per-digit: global offset of this block's run, then exclusive prefix over the 8 warps
-        const int d = threadIdx.x;
-        uint32_t run = (d < (1 << bits)) ? table[(size_t)d * nblocks + blockIdx.x] : 0u;
+    // ---- per digit: block count, exclusive prefix over the 8 warps, look-back over earlier tiles ----
+    const int d = threadIdx.x;
+    uint32_t cnt = 0;
 #pragma unroll
-        for (int w = 0; w < 8; w++) {
-            const uint32_t c = s_hist[w * RS_BINS + d];
-            s_hist[w * RS_BINS + d] = run;
-            run += c;
+    for (int ww = 0; ww < 8; ww++) {
+        const uint32_t c = s_hist[ww * RS_BINS + d];
+        s_hist[ww * RS_BINS + d] = cnt;
+        cnt += c;
+    }
+    volatile uint32_t* lb = lookback;
+    if (d < radix) lb[(size_t)bid * RS_BINS + d] = (bid == 0 ? LB_PREFIX : LB_AGG) | cnt;
+    uint32_t tot;
+    const uint32_t dstart = block_excl_scan<RS_THREADS>(cnt, s_warp, &tot);
+    const uint32_t gh = (d < radix) ? ghist[d] : 0u;
+    const uint32_t gstart = block_excl_scan<RS_THREADS>(gh, s_warp, &tot);
+    uint32_t ex = 0;
+    if (d < radix && bid > 0) {
+        int b = (int)bid - 1;
+        while (true) {
+            const uint32_t v = lb[(size_t)b * RS_BINS + d];
+            const uint32_t flag = v & ~LB_MASK;
+            if (flag == 0) continue;                 // not published yet: earlier tickets are resident, spin
+            ex += v & LB_MASK;
+            if (flag == LB_PREFIX) break;
+            b--;
         }
+        lb[(size_t)bid * RS_BINS + d] = LB_PREFIX | (ex + cnt);
     }
+    s_dstart[d] = dstart;
+    s_gbase[d] = gstart + ex - dstart;
     __syncthreads();
-    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const uint32_t* wb = s_hist + w * RS_BINS;
-    const size_t wbase = tile_base + (size_t)w * (32 * RS_ITEMS);
+
+    // ---- reorder by digit in shared memory ----
 #pragma unroll
     for (int r = 0; r < RS_ITEMS; r++) {
-        const size_t i = wbase + (size_t)r * 32 + lane;
-        if (i < n) {
-            const uint32_t d = (key[r] >> shift) & mask;
-            const uint32_t pos = wb[d] + rank[r];
-            kout[pos] = key[r];
-            vout[pos] = vin[i];
+        const int li = wofs + r * 32 + lane;
+        if (li < tile_n) {
+            const uint32_t dg = (key[r] >> shift) & mask;
+            const uint32_t lp = s_dstart[dg] + wh[dg] + rank[r];
+            s_keys[lp] = key[r];
+            s_vals[lp] = vin[tile_base + li];
+        }
+    }
+    __syncthreads();
+    // ---- contiguous runs out ----
+#pragma unroll
+    for (int k = 0; k < RS_ITEMS; k++) {
+        const int j = k * RS_THREADS + threadIdx.x;
+        if (j < tile_n) {
+            const uint32_t kk = s_keys[j];
+            const uint32_t pos = s_gbase[(kk >> shift) & mask] + (uint32_t)j;
+            kout[pos] = kk;
+            vout[pos] = s_vals[j];
         }
     }
 }
 
+// `table` holds [0,256) the pass's global digit histogram, [256] the ticket counter, [512, 512 + 256*tiles) the look-back table
 void radix_pass_u32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, size_t n,
                     int shift, int bits, uint32_t* table, uint32_t* scan_tmp, cudaStream_t st) {
+    (void)scan_tmp;
     if (n == 0) return;
     const unsigned nb = (unsigned)rs_blocks(n);
-    const size_t tbl = (size_t)nb * (1u << bits);
-    rs_hist_kernel<<<nb, RS_THREADS, 0, st>>>(kin, n, shift, bits, table, nb);
-    scan_exclusive_u32(table, table, tbl, scan_tmp, nullptr, st);
-    rs_scatter_kernel<<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, table, nb);
+    cudaMemsetAsync(table, 0, (512 + (size_t)nb * RS_BINS) * sizeof(uint32_t), st);
+    const unsigned hb = (unsigned)min((size_t)(148 * 8), (n / 4 + RS_THREADS - 1) / RS_THREADS + 1);
+    rs_hist_kernel<<<hb, RS_THREADS, 0, st>>>(kin, n, shift, bits, table);
+    rs_sweep_kernel<<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, table, table + 256, table + 512);
     count_launch(2);
 }
 

@@ -55,7 +55,7 @@ struct GeomState {
     uint32_t* vals[2];         // P each: Gaussian ids, ping-pong
     uint32_t* tt_sorted;       // P: tiles_touched in depth order
     uint32_t* offsets;         // P: exclusive scan of tt_sorted
-    uint32_t* table;           // rs_blocks(P) * RS_BINS
+    uint32_t* table;           // rs_blocks(P) * RS_BINS + 512 (digit histogram, ticket, look-back table)
     uint32_t* scan_tmp;        // block sums for the scans over P-sized / table-sized arrays
     uint32_t* total;           // 1: num_rendered on the device
     int* radii_internal;       // P: used when the caller passes radii == NULL (rasterizer_impl.cu:262-265)
@@ -69,7 +69,7 @@ struct GeomState {
         g.vals[0] = c.take<uint32_t>(P); g.vals[1] = c.take<uint32_t>(P);
         g.tt_sorted = c.take<uint32_t>(P);
         g.offsets = c.take<uint32_t>(P);
-        size_t tbl = rs_blocks(P) * RS_BINS;
+        size_t tbl = rs_blocks(P) * RS_BINS + 512;
         g.table = c.take<uint32_t>(tbl);
         size_t big = tbl > P ? tbl : P;
         g.scan_tmp = c.take<uint32_t>(scan_blocks(big) + 1);
@@ -83,14 +83,14 @@ struct GeomState {
 struct BinState {
     uint32_t* vals[2];         // R each; vals[0] is the final point_list
     uint32_t* keys[2];         // R each: tile ids, ping-pong
-    uint32_t* table;           // rs_blocks(R) * RS_BINS
+    uint32_t* table;           // rs_blocks(R) * RS_BINS + 512
     uint32_t* scan_tmp;
     size_t bytes;
     static BinState carve(char* base, size_t R) {
         BinState b; Carver c(base);
         b.vals[0] = c.take<uint32_t>(R); b.vals[1] = c.take<uint32_t>(R);
         b.keys[0] = c.take<uint32_t>(R); b.keys[1] = c.take<uint32_t>(R);
-        size_t tbl = rs_blocks(R) * RS_BINS;
+        size_t tbl = rs_blocks(R) * RS_BINS + 512;
         b.table = c.take<uint32_t>(tbl);
         b.scan_tmp = c.take<uint32_t>(scan_blocks(tbl) + 1);
         b.bytes = align_up(c.off, 256) + 256;
