@@ -184,6 +184,8 @@ def run_gpu(args):
     local = int(os.environ.get("LOCAL_RANK", "0"))
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"           # keep stdout to the one JSON line
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     device = torch.device("cuda", local)
@@ -202,12 +204,18 @@ def run_gpu(args):
     lib = GsrLib() if args.impl == "b200" else None
     hbm_peak, peak_src, sm_max = peaks()
 
+    # N > 1, this implementation: the fused exchange lives inside backward() (peer-mapped dL/dRGB blocks + one kernel
+    # for the SH block, one NCCL all-reduce for the 14 small floats).  The reference arm all-reduces its tensors with NCCL.
+    fused = world > 1 and args.impl == "b200" and do_bwd and not args.plain_allreduce
+    if fused:
+        MG.enable_multiview_training(P, device)
+
     def step_device():
         view.zero_grad()
         color, radii = view.forward()
         if do_bwd:
             color.backward(dL)
-            if world > 1:
+            if world > 1 and not fused:
                 MG.allreduce_gradients(view.grads())
         return color
 
@@ -286,7 +294,7 @@ def run_gpu(args):
         if do_bwd:
             loss = (color * dL).sum()
             loss.backward()
-            if world > 1:
+            if world > 1 and not fused:
                 MG.allreduce_gradients(view.grads())
             loss_host.copy_(loss.detach().view(1), non_blocking=True)
         else:
@@ -307,7 +315,8 @@ def run_gpu(args):
         "impl": args.impl,
         "config": {"workload": "%s: %d Gaussians, SH degree %d (M=%d), %dx%d, %s, 1 view per GPU per step%s" % (
             args.workload, P, deg, M, W, H, "fwd+bwd" if do_bwd else "forward only",
-            "" if world == 1 else ", NCCL all-reduce of per-Gaussian gradients"),
+            "" if world == 1 else (", fused SH-gradient exchange over peer memory + NCCL all-reduce of the 14 small floats" if fused
+                                   else ", NCCL all-reduce of per-Gaussian gradients")),
             "P": P, "width": W, "height": H, "sh_degree": deg, "num_rendered": R, "visible": visible,
             "cache": "inputs larger than L2 (%.0f MB of Gaussian parameters per step vs 126 MB L2)" % (P * (3 + 3 + 4 + 1 + 3 * M) * 4 / 1e6)},
         "fwd_ms": fwd_ms, "bwd_ms": bwd_ms,
@@ -425,6 +434,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--plain-allreduce", action="store_true", help="N > 1: one NCCL all-reduce of the whole gradient arena "
+                    "instead of the fused SH-gradient exchange")
     args = ap.parse_args()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.gpus > 1 and world == 1:

@@ -276,8 +276,29 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     pb.grad_acc = acc;
     pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dconic = a->dL_dconic; pb.dL_dopacity = a->dL_dopacity; pb.dL_dcolor = a->dL_dcolor;
     pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh; pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
+    pb.dL_drgb = a->dL_drgb; pb.skip_dsh = (a->dL_drgb != nullptr && a->skip_dL_dsh) ? 1 : 0;
     { StageTimer t(ST_PREPROCESS_BWD, st); launch_preprocess_backward(pb, st); }
     GSR_STAGE("preprocess backward", st, a->debug);
+    return GSR_OK;
+}
+
+int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* peer_blocks, const float* means3D,
+                          float* dL_dsh, void* cuda_stream) {
+    if (P < 0 || D < 0 || D > 3 || M < (D + 1) * (D + 1) || n_views < 1 || n_views > GSR_MAX_VIEWS)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "bad sizes");
+    if (P == 0) return GSR_OK;
+    if (!peer_blocks || !means3D || !dL_dsh) return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
+    MultiviewShArgs a;
+    a.P = P; a.D = D; a.M = M; a.n_views = n_views; a.means3D = means3D; a.dL_dsh = dL_dsh;
+    for (int v = 0; v < 16; v++) a.blocks[v] = nullptr;
+    for (int v = 0; v < n_views; v++) {
+        if (!peer_blocks[v] || ((size_t)peer_blocks[v] & 15)) return fail(GSR_ERR_INVALID_ARGUMENT, "peer block missing or not 16-byte aligned");
+        a.blocks[v] = peer_blocks[v];
+    }
+    if ((size_t)dL_dsh & 15) return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dsh not 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_multiview_sh_grad(a, st);
+    GSR_STAGE("multiview sh grad", st, 0);
     return GSR_OK;
 }
 

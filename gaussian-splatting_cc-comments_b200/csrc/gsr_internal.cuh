@@ -15,8 +15,8 @@ namespace gsr {
 
 // ---- per-Gaussian packed record consumed by both blending kernels (48 B, 3 x float4) ---------
 //   a = (mean2D.x, mean2D.y, conic.x, conic.y)
-//   b = (conic.z, opacity, r, g)
-//   c = (b, ext_x, ext_y, power_thr)
+//   b = (conic.z, power_thr, opacity, r)      a + b: everything up to the alpha test
+//   c = (g, b, ext_x, ext_y)                  c.xy: only for contributing pairs; c.zw: only for the warp cull
 // ext_x/ext_y: conservative half-extents (pixels) of the region where alpha can reach 1/255
 //              (negative => can never contribute); power_thr: `power < power_thr` implies
 //              alpha < 1/255 without evaluating exp.
@@ -168,7 +168,17 @@ struct PreprocessBwdArgs {
     const float* grad_acc;     // (P,12)
     float* dL_dmean2D; float* dL_dconic; float* dL_dopacity; float* dL_dcolor;
     float* dL_dmean3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;
+    float* dL_drgb;            // optional (P,3): clamp-masked colour gradient (multi-view exchange)
+    int skip_dsh;              // leave dL_dsh untouched
 };
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st);
+
+struct MultiviewShArgs {
+    int P, D, M, n_views;
+    const float* blocks[16];   // per view: campos (4 floats) then (P,3) masked colour gradients, peer-mapped
+    const float* means3D;
+    float* dL_dsh;
+};
+void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st);
 
 }  // namespace gsr

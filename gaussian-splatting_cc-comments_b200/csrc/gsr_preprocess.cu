@@ -151,8 +151,8 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
                 }
                 float4* rec = a.packed + 3 * (size_t)idx;
                 rec[0] = make_float4(px, py, conx, cony);
-                rec[1] = make_float4(conz, opacity, rgb[0], rgb[1]);
-                rec[2] = make_float4(rgb[2], ext_x, ext_y, thr);
+                rec[1] = make_float4(conz, thr, opacity, rgb[0]);
+                rec[2] = make_float4(rgb[1], rgb[2], ext_x, ext_y);
                 a.clamped[idx] = (uint8_t)clampbits;
 
                 out_radius = irad;

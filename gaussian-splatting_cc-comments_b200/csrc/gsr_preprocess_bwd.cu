@@ -9,6 +9,7 @@
 // stored in the forward and re-read here.  HBM-bound.
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
+#include "gsr_smem.cuh"
 
 namespace gsr {
 
@@ -78,6 +79,70 @@ __device__ __forceinline__ F3 sh_backward(int deg, const float* sh, F3 dir_orig,
     return dnormvdv(dir_orig, dL_ddir);
 }
 
+// SH backward on a shared-memory row, in place: the row holds sh[0..3K) on entry and dL_dsh[0..3K) (zero
+// padded to a multiple of 4 floats) on exit.  Same derivative as sh_backward, written as a weighted sum
+// dRGB/d{x,y,z} = sum_i w{x,y,z}_i * sh_i so that the row is consumed and overwritten one 16-byte chunk at
+// a time (no 48-float register copy, no run-time indexed arrays).  Weights are d(basis_i)/d{x,y,z} of
+// backward.cu:60-128; structurally zero ones are skipped at compile time.
+template <int DEG>
+__device__ __forceinline__ F3 sh_backward_row(uint32_t row, F3 dir_orig, F3 dRGB) {
+    constexpr int K = (DEG + 1) * (DEG + 1);
+    constexpr int NF = 3 * K, NV = (NF + 3) / 4;
+    const float len = __fsqrt_rn(fmar(dir_orig.z, dir_orig.z, fmar(dir_orig.x, dir_orig.x, mulr(dir_orig.y, dir_orig.y))));
+    const float x = __fdiv_rn(dir_orig.x, len), y = __fdiv_rn(dir_orig.y, len), z = __fdiv_rn(dir_orig.z, len);
+    float k[16], wx[16], wy[16], wz[16];
+    sh_basis(DEG, x, y, z, k);
+#pragma unroll
+    for (int i = 0; i < 16; i++) { wx[i] = 0.f; wy[i] = 0.f; wz[i] = 0.f; }
+    if (DEG > 0) { wy[1] = -GSR_SH_C1; wz[2] = GSR_SH_C1; wx[3] = -GSR_SH_C1; }
+    if (DEG > 1) {
+        wx[4] = GSR_SH_C2_0 * y; wy[4] = GSR_SH_C2_0 * x;
+        wy[5] = GSR_SH_C2_1 * z; wz[5] = GSR_SH_C2_1 * y;
+        wx[6] = GSR_SH_C2_2 * 2.f * -x; wy[6] = GSR_SH_C2_2 * 2.f * -y; wz[6] = GSR_SH_C2_2 * 2.f * 2.f * z;
+        wx[7] = GSR_SH_C2_3 * z; wz[7] = GSR_SH_C2_3 * x;
+        wx[8] = GSR_SH_C2_4 * 2.f * x; wy[8] = GSR_SH_C2_4 * 2.f * -y;
+    }
+    if (DEG > 2) {
+        const float xx = x * x, yy = y * y, zz = z * z, xy = x * y, yz = y * z, xz = x * z;
+        wx[9] = GSR_SH_C3_0 * 3.f * 2.f * xy; wy[9] = GSR_SH_C3_0 * 3.f * (xx - yy);
+        wx[10] = GSR_SH_C3_1 * yz; wy[10] = GSR_SH_C3_1 * xz; wz[10] = GSR_SH_C3_1 * xy;
+        wx[11] = GSR_SH_C3_2 * -2.f * xy; wy[11] = GSR_SH_C3_2 * (-3.f * yy + 4.f * zz - xx); wz[11] = GSR_SH_C3_2 * 4.f * 2.f * yz;
+        wx[12] = GSR_SH_C3_3 * -3.f * 2.f * xz; wy[12] = GSR_SH_C3_3 * -3.f * 2.f * yz; wz[12] = GSR_SH_C3_3 * 3.f * (2.f * zz - xx - yy);
+        wx[13] = GSR_SH_C3_4 * (-3.f * xx + 4.f * zz - yy); wy[13] = GSR_SH_C3_4 * -2.f * xy; wz[13] = GSR_SH_C3_4 * 4.f * 2.f * xz;
+        wx[14] = GSR_SH_C3_5 * 2.f * xz; wy[14] = GSR_SH_C3_5 * -2.f * yz; wz[14] = GSR_SH_C3_5 * (xx - yy);
+        wx[15] = GSR_SH_C3_6 * 3.f * (xx - yy); wy[15] = GSR_SH_C3_6 * -3.f * 2.f * xy;
+    }
+    // structural zeros (compile-time): which weights exist at all
+    constexpr unsigned HAS_X = 0xFFD8u /* i = 3,4,6,7,8,9..15 */, HAS_Y = 0xFF72u /* 1,4,5,6,8,9..15 */, HAS_Z = 0x7CE4u /* 2,5,6,7,10..14 */;
+    float dxs[3] = {0.f, 0.f, 0.f}, dys[3] = {0.f, 0.f, 0.f}, dzs[3] = {0.f, 0.f, 0.f};
+    const float dr[3] = {dRGB.x, dRGB.y, dRGB.z};
+#pragma unroll
+    for (int c4 = 0; c4 < NV; c4++) {
+        const float4 v = lds128<0>(row + c4 * 16);
+        const float e[4] = {v.x, v.y, v.z, v.w};
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            const int f = 4 * c4 + j;
+            const int i = f / 3, ch = f % 3;
+            if (f < NF) {
+                if (i > 0) {
+                    if ((HAS_X >> i) & 1u) dxs[ch] = fmaf(wx[i], e[j], dxs[ch]);
+                    if ((HAS_Y >> i) & 1u) dys[ch] = fmaf(wy[i], e[j], dys[ch]);
+                    if ((HAS_Z >> i) & 1u) dzs[ch] = fmaf(wz[i], e[j], dzs[ch]);
+                }
+                o[j] = k[i] * dr[ch];
+            } else {
+                o[j] = 0.f;
+            }
+        }
+        sts128<0>(row + c4 * 16, make_float4(o[0], o[1], o[2], o[3]));
+    }
+    const F3 dL_ddir = f3(dxs[0] * dr[0] + dxs[1] * dr[1] + dxs[2] * dr[2], dys[0] * dr[0] + dys[1] * dr[1] + dys[2] * dr[2],
+                          dzs[0] * dr[0] + dzs[1] * dr[1] + dzs[2] * dr[2]);
+    return dnormvdv(dir_orig, dL_ddir);
+}
+
 // computeCov3D backward (backward.cu:281-344)
 __device__ __forceinline__ void cov3d_backward(float sx0, float sy0, float sz0, float mod, float4 q, const float* g /* dL_dcov3D[6] */,
                                                float* dL_dscale, float* dL_drot) {
@@ -108,7 +173,7 @@ __device__ __forceinline__ void cov3d_backward(float sx0, float sy0, float sz0, 
 }
 
 // Everything one Gaussian produces except dL_dsh (which goes straight to its row pointer).
-struct BwdOut { float g[9]; float dmean[3]; float dcov[6]; float dscale[3]; float drot[4]; };
+struct BwdOut { float g[9]; float dmean[3]; float dcov[6]; float dscale[3]; float drot[4]; float drgb[3]; };
 
 // The per-Gaussian backward math.  `sh_row` / `dsh_row` are this Gaussian's SH coefficients and SH-gradient
 // row: global pointers in the generic kernel, the same shared-memory row in the staged kernel.
@@ -120,7 +185,7 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
 #pragma unroll
     for (int i = 0; i < 9; i++) o.g[i] = 0.f;
 #pragma unroll
-    for (int i = 0; i < 3; i++) { o.dmean[i] = 0.f; o.dscale[i] = 0.f; }
+    for (int i = 0; i < 3; i++) { o.dmean[i] = 0.f; o.dscale[i] = 0.f; o.drgb[i] = 0.f; }
 #pragma unroll
     for (int i = 0; i < 6; i++) o.dcov[i] = 0.f;
 #pragma unroll
@@ -201,7 +266,19 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
         const uint32_t cl = a.clamped[idx];
         const F3 dRGB = f3((cl & 1) ? 0.f : g[6], (cl & 2) ? 0.f : g[7], (cl & 4) ? 0.f : g[8]);
         const F3 dir = f3(subr(mx, V[32]), subr(my, V[33]), subr(mz, V[34]));
-        const F3 dm = sh_backward<SMEM>(a.D, sh_row, dir, dRGB, dsh_row);
+        o.drgb[0] = dRGB.x; o.drgb[1] = dRGB.y; o.drgb[2] = dRGB.z;
+        F3 dm;
+        if (SMEM) {
+            const uint32_t row = smem_addr(sh_row);
+            switch (a.D) {
+                case 0: dm = sh_backward_row<0>(row, dir, dRGB); break;
+                case 1: dm = sh_backward_row<1>(row, dir, dRGB); break;
+                case 2: dm = sh_backward_row<2>(row, dir, dRGB); break;
+                default: dm = sh_backward_row<3>(row, dir, dRGB); break;
+            }
+        } else {
+            dm = sh_backward<false>(a.D, sh_row, dir, dRGB, dsh_row);
+        }
         sh_written = (a.D + 1) * (a.D + 1);
         dmean[0] += dm.x; dmean[1] += dm.y; dmean[2] += dm.z;
     }
@@ -239,6 +316,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
 #pragma unroll
     for (int i = 0; i < 4; i++) a.dL_drot[4 * (size_t)idx + i] = o.drot[i];
     if (dsh) for (int i = 3 * sh_written; i < 3 * a.M; i++) dsh[i] = 0.f;
+    if (a.dL_drgb) { a.dL_drgb[i3] = o.drgb[0]; a.dL_drgb[i3 + 1] = o.drgb[1]; a.dL_drgb[i3 + 2] = o.drgb[2]; }
 }
 
 // ---- staged kernel: the common case (3*M a multiple of 4, 16-byte aligned tensors) ------------------------
@@ -248,7 +326,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
 // culled Gaussians and for coefficients beyond the active degree).  The 27 other floats per Gaussian are
 // staged the same way, so every global store instruction of a warp covers one contiguous 512-byte span.
 constexpr int PB = 128;
-constexpr int PB_OUT = 27 * PB;     // mean2D 3 | conic 4 | opacity 1 | colour 3 | mean3D 3 | cov3D 6 | scale 3 | rot 4
+constexpr int PB_OUT = 30 * PB;     // mean2D 3 | conic 4 | opacity 1 | colour 3 | mean3D 3 | cov3D 6 | scale 3 | rot 4 | masked rgb 3
 
 __device__ __forceinline__ void copy_out(float* __restrict__ dst, const float* __restrict__ src, int n) {
     int n4 = ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) ? (n >> 2) : 0;
@@ -259,8 +337,9 @@ __device__ __forceinline__ void copy_out(float* __restrict__ dst, const float* _
 __global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwdArgs a, int S /* smem row stride, floats */) {
     __shared__ float s_cam[36];
     __shared__ uint8_t s_vis[PB];
-    __shared__ __align__(16) float s_out[PB_OUT];
-    extern __shared__ __align__(16) float s_sh[];
+    extern __shared__ __align__(16) float s_dyn[];     // SH rows (PB x S), later re-used for the 27 other outputs
+    float* s_sh = s_dyn;
+    float* s_out = s_dyn;
     load_camera(a, s_cam);
     const int row0 = blockIdx.x * PB;
     const int nrows = min(PB, a.P - row0);
@@ -271,6 +350,7 @@ __global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwd
     __syncthreads();
     const int L = 3 * a.M;
     const int Kf = 3 * (a.D + 1) * (a.D + 1);               // live floats per row
+    const int Kf4 = (Kf + 3) & ~3;
     const bool has_sh = a.shs != nullptr;
     const int qstep = L ? (4 * PB) / L : 0, rstep = L ? (4 * PB) % L : 0;
     if (has_sh) {
@@ -278,20 +358,32 @@ __global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwd
         const int n4 = nrows * L / 4;
         int f = 4 * t, row = f / L, col = f - row * L;
         for (int e4 = t; e4 < n4; e4 += PB) {
-            if (s_vis[row] && col < Kf) {
-                const float4 v = __ldg(src + e4);
-                float* d = s_sh + row * S + col;
-                d[0] = v.x; d[1] = v.y; d[2] = v.z; d[3] = v.w;
-            }
+            if (s_vis[row] && col < Kf4) *reinterpret_cast<float4*>(s_sh + row * S + col) = __ldg(src + e4);
             row += qstep; col += rstep;
             if (col >= L) { col -= L; row++; }
         }
         __syncthreads();
     }
+    BwdOut o;
     if (valid) {
-        BwdOut o;
         float* myrow = s_sh + t * S;
         bwd_one<true>(a, idx, s_cam, s_cam + 16, myrow, myrow, o);
+    }
+    __syncthreads();
+    if (a.dL_dsh != nullptr && L > 0 && !a.skip_dsh) {
+        float4* dst = reinterpret_cast<float4*>(a.dL_dsh + (size_t)row0 * L);
+        const int n4 = nrows * L / 4;
+        int f = 4 * t, row = f / L, col = f - row * L;
+        for (int e4 = t; e4 < n4; e4 += PB) {
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (has_sh && s_vis[row] && col < Kf4) v = *reinterpret_cast<const float4*>(s_sh + row * S + col);
+            dst[e4] = v;
+            row += qstep; col += rstep;
+            if (col >= L) { col -= L; row++; }
+        }
+    }
+    __syncthreads();                                    // SH rows are out: the same memory now stages the rest
+    if (valid) {
         s_out[3 * t] = o.g[0]; s_out[3 * t + 1] = o.g[1]; s_out[3 * t + 2] = 0.f;
         reinterpret_cast<float4*>(s_out + 3 * PB)[t] = make_float4(o.g[2], o.g[3], 0.f, o.g[4]);
         s_out[7 * PB + t] = o.g[5];
@@ -301,6 +393,7 @@ __global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwd
         for (int i = 0; i < 6; i++) s_out[14 * PB + 6 * t + i] = o.dcov[i];
         s_out[20 * PB + 3 * t] = o.dscale[0]; s_out[20 * PB + 3 * t + 1] = o.dscale[1]; s_out[20 * PB + 3 * t + 2] = o.dscale[2];
         reinterpret_cast<float4*>(s_out + 23 * PB)[t] = make_float4(o.drot[0], o.drot[1], o.drot[2], o.drot[3]);
+        s_out[27 * PB + 3 * t] = o.drgb[0]; s_out[27 * PB + 3 * t + 1] = o.drgb[1]; s_out[27 * PB + 3 * t + 2] = o.drgb[2];
     }
     __syncthreads();
     copy_out(a.dL_dmean2D + (size_t)row0 * 3, s_out, nrows * 3);
@@ -311,36 +404,148 @@ __global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwd
     copy_out(a.dL_dcov3D + (size_t)row0 * 6, s_out + 14 * PB, nrows * 6);
     copy_out(a.dL_dscale + (size_t)row0 * 3, s_out + 20 * PB, nrows * 3);
     copy_out(a.dL_drot + (size_t)row0 * 4, s_out + 23 * PB, nrows * 4);
-    if (a.dL_dsh != nullptr && L > 0) {
-        float4* dst = reinterpret_cast<float4*>(a.dL_dsh + (size_t)row0 * L);
-        const int n4 = nrows * L / 4;
-        const bool live = has_sh;
-        int f = 4 * t, row = f / L, col = f - row * L;
-        for (int e4 = t; e4 < n4; e4 += PB) {
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (live && s_vis[row] && col < Kf) {
-                const float* sp = s_sh + row * S + col;
-                v.x = sp[0];
-                v.y = (col + 1 < Kf) ? sp[1] : 0.f;
-                v.z = (col + 2 < Kf) ? sp[2] : 0.f;
-                v.w = (col + 3 < Kf) ? sp[3] : 0.f;
-            }
-            dst[e4] = v;
-            row += qstep; col += rstep;
-            if (col >= L) { col -= L; row++; }
-        }
-    }
+    if (a.dL_drgb) copy_out(a.dL_drgb + (size_t)row0 * 3, s_out + 27 * PB, nrows * 3);
 }
 
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
     const int L = 3 * a.M;
-    const int S = (L % 2 == 0) ? L + 1 : L;
-    const size_t dyn = a.shs ? (size_t)PB * S * sizeof(float) : 0;
+    const int S = ((L / 4) % 2 == 1 || L == 0) ? L : L + 4;      // 16-byte rows, odd number of 16-byte words: conflict-free
+    size_t dyn = (size_t)PB_OUT * sizeof(float);
+    if (a.shs && (size_t)PB * S * sizeof(float) > dyn) dyn = (size_t)PB * S * sizeof(float);
     const bool aligned = (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0;
-    const bool staged = (L % 4 == 0) && aligned && dyn <= 32 * 1024 && (a.M == 0 || a.dL_dsh != nullptr);
+    const bool staged = (L % 4 == 0) && aligned && dyn <= 40 * 1024 && (a.M == 0 || a.dL_dsh != nullptr);
     if (staged) preprocess_bwd_kernel_staged<<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
     else preprocess_bwd_kernel_generic<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    count_launch(1);
+}
+
+}  // namespace gsr
+
+// ------------------------------------------------------------------------------------------------
+// Multi-view SH-gradient exchange fused with its producer math (include/gsr.h: gsr_multiview_sh_grad).
+// Each rank's backward leaves 12 bytes per Gaussian (clamp-masked dL/dRGB) and its camera position in a
+// peer-mapped block.  One kernel per rank pulls every rank's block over NVLink with plain coalesced 16-byte
+// peer loads, rebuilds the SH basis for each view's direction and writes sum_v basis(dir_v) (x) dRGB_v as
+// coalesced 16-byte rows -- 12 B per Gaussian per view cross the links instead of the 12*M B an all-reduce of
+// dL_dsh moves twice.  128 Gaussians per block, staged through shared memory like the backward above.
+namespace gsr {
+
+constexpr int MV = 128;
+
+template <int DEG>
+__device__ __forceinline__ void mv_accumulate(float* acc, float x, float y, float z, float r, float g, float b) {
+    constexpr int K = (DEG + 1) * (DEG + 1);
+    float k[16];
+    sh_basis(DEG, x, y, z, k);
+#pragma unroll
+    for (int i = 0; i < K; i++) {
+        acc[3 * i] = fmaf(k[i], r, acc[3 * i]);
+        acc[3 * i + 1] = fmaf(k[i], g, acc[3 * i + 1]);
+        acc[3 * i + 2] = fmaf(k[i], b, acc[3 * i + 2]);
+    }
+}
+
+template <int DEG>
+__global__ void __launch_bounds__(MV) multiview_sh_grad_kernel(MultiviewShArgs a, int S) {
+    constexpr int K = (DEG + 1) * (DEG + 1);
+    constexpr int NF = 3 * K, NV = (NF + 3) / 4;
+    extern __shared__ __align__(16) float s_mv[];        // [n_views][MV*3] colour gradients, then MV rows of S floats
+    float* s_rgb = s_mv;
+    float* s_rows = s_mv + a.n_views * MV * 3;
+    __shared__ float s_campos[16 * 4];
+    const int row0 = blockIdx.x * MV;
+    const int nrows = min(MV, a.P - row0);
+    const int t = threadIdx.x;
+    if (t < a.n_views * 4) s_campos[t] = a.blocks[t >> 2][t & 3];
+    // ---- peer loads: each view's (nrows,3) slice is one contiguous span ----
+    const int n = nrows * 3, n4 = n >> 2;
+    for (int v = 0; v < a.n_views; v++) {
+        const float* src = a.blocks[v] + 4 + (size_t)row0 * 3;      // 16-byte aligned: row0 is a multiple of 128
+        float* dst = s_rgb + v * MV * 3;
+        for (int i = t; i < n4; i += MV) reinterpret_cast<float4*>(dst)[i] = reinterpret_cast<const float4*>(src)[i];
+        for (int i = 4 * n4 + t; i < n; i += MV) dst[i] = src[i];
+    }
+    __syncthreads();
+    if (t < nrows) {
+        float acc[NF];
+#pragma unroll
+        for (int i = 0; i < NF; i++) acc[i] = 0.f;
+        const size_t i3 = 3 * (size_t)(row0 + t);
+        const float mx = __ldg(a.means3D + i3), my = __ldg(a.means3D + i3 + 1), mz = __ldg(a.means3D + i3 + 2);
+        for (int v = 0; v < a.n_views; v++) {
+            const float r = s_rgb[v * MV * 3 + 3 * t], g = s_rgb[v * MV * 3 + 3 * t + 1], b = s_rgb[v * MV * 3 + 3 * t + 2];
+            if (r == 0.f && g == 0.f && b == 0.f) continue;         // culled / fully clamped in this view
+            // direction exactly as the forward and the single-view backward compute it (forward.cu:28-31)
+            const float dx = subr(mx, s_campos[4 * v]), dy = subr(my, s_campos[4 * v + 1]), dz = subr(mz, s_campos[4 * v + 2]);
+            const float len = __fsqrt_rn(fmar(dz, dz, fmar(dx, dx, mulr(dy, dy))));
+            mv_accumulate<DEG>(acc, __fdiv_rn(dx, len), __fdiv_rn(dy, len), __fdiv_rn(dz, len), r, g, b);
+        }
+        float* row = s_rows + t * S;
+#pragma unroll
+        for (int c = 0; c < NV; c++) {
+            float4 v4;
+            v4.x = acc[4 * c];
+            v4.y = (4 * c + 1 < NF) ? acc[4 * c + 1] : 0.f;
+            v4.z = (4 * c + 2 < NF) ? acc[4 * c + 2] : 0.f;
+            v4.w = (4 * c + 3 < NF) ? acc[4 * c + 3] : 0.f;
+            reinterpret_cast<float4*>(row)[c] = v4;
+        }
+    }
+    __syncthreads();
+    const int L = 3 * a.M;
+    float4* dst = reinterpret_cast<float4*>(a.dL_dsh + (size_t)row0 * L);
+    const int m4 = nrows * L / 4;
+    const int qstep = (4 * MV) / L, rstep = (4 * MV) % L;
+    int f = 4 * t, row = f / L, col = f - row * L;
+    for (int e4 = t; e4 < m4; e4 += MV) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (col < 4 * NV) v = *reinterpret_cast<const float4*>(s_rows + row * S + col);
+        dst[e4] = v;
+        row += qstep; col += rstep;
+        if (col >= L) { col -= L; row++; }
+    }
+}
+
+// fallback for shapes the staged kernel does not take (3*M not a multiple of 4): one thread per Gaussian
+__global__ void __launch_bounds__(256) multiview_sh_grad_kernel_generic(MultiviewShArgs a) {
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= a.P) return;
+    float acc[48];
+    for (int i = 0; i < 48; i++) acc[i] = 0.f;
+    const size_t i3 = 3 * (size_t)idx;
+    const float mx = __ldg(a.means3D + i3), my = __ldg(a.means3D + i3 + 1), mz = __ldg(a.means3D + i3 + 2);
+    const int K = (a.D + 1) * (a.D + 1);
+    for (int v = 0; v < a.n_views; v++) {
+        const float* blk = a.blocks[v];
+        const float r = blk[4 + i3], g = blk[4 + i3 + 1], b = blk[4 + i3 + 2];
+        if (r == 0.f && g == 0.f && b == 0.f) continue;
+        const float dx = subr(mx, blk[0]), dy = subr(my, blk[1]), dz = subr(mz, blk[2]);
+        const float len = __fsqrt_rn(fmar(dz, dz, fmar(dx, dx, mulr(dy, dy))));
+        float k[16];
+        sh_basis(a.D, __fdiv_rn(dx, len), __fdiv_rn(dy, len), __fdiv_rn(dz, len), k);
+        for (int i = 0; i < K; i++) { acc[3 * i] += k[i] * r; acc[3 * i + 1] += k[i] * g; acc[3 * i + 2] += k[i] * b; }
+    }
+    float* out = a.dL_dsh + (size_t)idx * a.M * 3;
+    for (int i = 0; i < 3 * a.M; i++) out[i] = (i < 3 * K) ? acc[i] : 0.f;
+}
+
+void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st) {
+    if (a.P <= 0) return;
+    const int L = 3 * a.M;
+    const int S = ((L / 4) % 2 == 1) ? L : L + 4;
+    const size_t dyn = ((size_t)a.n_views * MV * 3 + (size_t)MV * S) * sizeof(float);
+    if (L % 4 == 0 && dyn <= 44 * 1024) {
+        const unsigned grid = (a.P + MV - 1) / MV;
+        switch (a.D) {
+            case 0: multiview_sh_grad_kernel<0><<<grid, MV, dyn, st>>>(a, S); break;
+            case 1: multiview_sh_grad_kernel<1><<<grid, MV, dyn, st>>>(a, S); break;
+            case 2: multiview_sh_grad_kernel<2><<<grid, MV, dyn, st>>>(a, S); break;
+            default: multiview_sh_grad_kernel<3><<<grid, MV, dyn, st>>>(a, S); break;
+        }
+    } else {
+        multiview_sh_grad_kernel_generic<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    }
     count_launch(1);
 }
 

@@ -14,10 +14,12 @@
 // cross-pixel summation order differs (gradient tolerance 1e-4 relative L2).
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
+#include "gsr_smem.cuh"
 
 namespace gsr {
 
 constexpr int RBB = GSR_TILE_PIX;
+constexpr int BOFF_B = RBB * 16, BOFF_C = 2 * RBB * 16, BOFF_ID = 3 * RBB * 16;   // byte offsets of the b / c / id planes
 
 template <int N>
 __device__ __forceinline__ void reduce_scatter_step(float* v, int bit, bool upper) {
@@ -29,16 +31,14 @@ __device__ __forceinline__ void reduce_scatter_step(float* v, int bit, bool uppe
     }
 }
 
-__global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+__global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                                                          int W, int H, int grid_x, int row_begin,
                                                          const float4* __restrict__ packed, const float* __restrict__ bg,
                                                          const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
                                                          const float* __restrict__ dL_dpixels, float* __restrict__ grad_acc) {
-    __shared__ float4 s_a[RBB];
-    __shared__ float4 s_b[RBB];
-    __shared__ float4 s_c[RBB];
-    __shared__ uint32_t s_id[RBB];
+    __shared__ __align__(16) float4 s_rec[3 * RBB + RBB / 4];    // planes a | b | c of the staged records, then their ids
     __shared__ uint32_t s_max[8];
+    const uint32_t sb = smem_addr(s_rec);
 
     const int tile_x = blockIdx.x, tile_y = blockIdx.y + row_begin;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -77,6 +77,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
     for (int w = 0; w < 8; w++) bmax = max(bmax, (int)s_max[w]);
     const int rounds = (bmax + RBB - 1) / RBB;
 
+    const uint32_t my_slot = sb + threadIdx.x * 16;
     for (int i = 0; i < rounds; i++) {
         __syncthreads();
         const int first_pos = bmax - 1 - i * RBB;          // position staged by thread 0
@@ -84,47 +85,52 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
         if (mypos >= 0) {
             const uint32_t id = point_list[range.x + mypos];
             const float4* rec = packed + 3 * (size_t)id;
-            s_id[threadIdx.x] = id;
-            s_a[threadIdx.x] = __ldg(rec);
-            s_b[threadIdx.x] = __ldg(rec + 1);
-            s_c[threadIdx.x] = __ldg(rec + 2);
+            const float4 ra = __ldg(rec), rb = __ldg(rec + 1), rc = __ldg(rec + 2);
+            sts128<0>(my_slot, ra);
+            sts128<BOFF_B>(my_slot, rb);
+            sts128<BOFF_C>(my_slot, rc);
+            sts32u<BOFF_ID>(sb + threadIdx.x * 4, id);
         }
         __syncthreads();
         const int count = min(RBB, first_pos + 1);
         if (first_pos - (count - 1) >= wmax) continue;      // whole batch is behind this warp's last contributor
         for (int cbase = 0; cbase < count; cbase += 32) {
-            const int jj = cbase + lane;
+            // lane l tests staged Gaussian cbase + 31 - l: the next one to replay is the highest set ballot bit
+            const int jj = cbase + 31 - lane;
             bool hit = false;
             if (jj < count && first_pos - jj < wmax) {
-                const float4 a = s_a[jj];
-                const float4 c = s_c[jj];
-                const float ddx = fmaxf(fmaxf(fx0 - a.x, a.x - fx1), 0.0f);
-                const float ddy = fmaxf(fmaxf(fy0 - a.y, a.y - fy1), 0.0f);
-                hit = (ddx <= c.y) && (ddy <= c.z);
+                const uint32_t ja = sb + (uint32_t)jj * 16;
+                const float2 xy = lds64<0>(ja);
+                const float2 ext = lds64<BOFF_C + 8>(ja);
+                const float ddx = fmaxf(fmaxf(fx0 - xy.x, xy.x - fx1), 0.0f);
+                const float ddy = fmaxf(fmaxf(fy0 - xy.y, xy.y - fy1), 0.0f);
+                hit = (ddx <= ext.x) && (ddy <= ext.y);
             }
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
-                const int j = cbase + (__ffs(m) - 1);
-                m &= m - 1;
+                const int top = 31 - __clz(m);
+                m ^= 1u << top;
+                const int j = cbase + 31 - top;
                 const int pos = first_pos - j;
-                const float4 a = s_a[j];
-                const float4 b = s_b[j];
-                const float4 c = s_c[j];
+                const uint32_t ja = sb + (uint32_t)j * 16;
                 float v[8];
                 float v8 = 0.f;
 #pragma unroll
                 for (int q = 0; q < 8; q++) v[q] = 0.f;
                 bool contrib = false;
                 if (pos < last_contributor) {
+                    const float4 a = lds128<0>(ja);         // x, y, conic.x, conic.y
+                    const float4 b = lds128<BOFF_B>(ja);    // conic.z, power_thr, opacity, r
                     // same expression as the forward, so the same pairs pass the tests
                     const float dx = subr(a.x, pixfx), dy = subr(a.y, pixfy);
                     const float s = fmar(dx, mulr(dx, a.z), mulr(dy, mulr(dy, b.x)));
                     const float power = fmar(s, -0.5f, -mulr(dy, mulr(dx, a.w)));
-                    if (!(power > 0.0f) && !(power < c.w)) {
+                    if (!(power > 0.0f) && !(power < b.y)) {
                         const float G = expf(power);
-                        const float alpha = fminf(0.99f, mulr(b.y, G));
+                        const float alpha = fminf(0.99f, mulr(b.z, G));
                         if (!(alpha < 1.0f / 255.0f)) {
                             contrib = true;
+                            const float2 gb = lds64<BOFF_C>(ja);   // g, b
                             const float one_m_alpha = 1.0f - alpha;
                             const float inv = __frcp_rn(one_m_alpha);
                             T = T * inv;                                   // backward.cu:534
@@ -133,7 +139,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
                             ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0;
                             ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1;
                             ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2;
-                            lc0 = b.z; lc1 = b.w; lc2 = c.x;
+                            lc0 = b.w; lc1 = gb.x; lc2 = gb.y;
                             float dL_dalpha = (lc0 - ar0) * dpix0 + (lc1 - ar1) * dpix1 + (lc2 - ar2) * dpix2;
                             v[6] = dchannel_dcolor * dpix0;
                             v[7] = dchannel_dcolor * dpix1;
@@ -141,7 +147,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
                             dL_dalpha *= T;
                             last_alpha = alpha;
                             dL_dalpha += (-T_final * inv) * bg_dot_dpixel;  // backward.cu:571-574
-                            const float dL_dG = b.y * dL_dalpha;
+                            const float dL_dG = b.z * dL_dalpha;
                             const float gdx = G * dx, gdy = G * dy;
                             const float dG_ddelx = -gdx * a.z - gdy * a.w;
                             const float dG_ddely = -gdy * b.x - gdx * a.w;
@@ -163,7 +169,7 @@ __global__ void __launch_bounds__(256) render_bwd_kernel(const uint2* __restrict
                     r += __shfl_xor_sync(0xffffffffu, r, 1);
 #pragma unroll
                     for (int d = 16; d > 0; d >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, d);
-                    float* dst = grad_acc + 12 * (size_t)s_id[j];
+                    float* dst = grad_acc + 12 * (size_t)lds32u<BOFF_ID>(sb + (uint32_t)j * 4);
                     if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), r);
                     else if (lane == 1) atomicAdd(dst + 8, v8);
                 }

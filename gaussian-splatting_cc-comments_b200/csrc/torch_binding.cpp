@@ -87,7 +87,8 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
                                const torch::Tensor& dL_dout_color, const torch::Tensor& sh, const int degree,
                                const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
                                const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
-                               const int tile_row_begin, const int tile_row_end) {
+                               const int tile_row_begin, const int tile_row_end,
+                               const c10::optional<torch::Tensor>& drgb_block, const bool skip_dsh) {
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
     const c10::cuda::CUDAGuard guard(means3D.device());
     const auto dev = means3D.device();
@@ -96,14 +97,15 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
     int64_t M = 0;
     if (sh.numel() != 0) M = sh.size(1);
     auto fopt = means3D.options().dtype(torch::kFloat32);
-    // one flat gradient arena; per-Gaussian widths: mean3D 3, mean2D 3, opacity 1, sh 3M, scale 3, rot 4, colour 3, cov3D 6, conic 4
-    const int64_t widths[9] = {3, 3, 1, 3 * M, 3, 4, 3, 6, 4};
+    // one flat gradient arena; per-Gaussian widths: mean3D 3, mean2D 3, opacity 1, scale 3, rot 4 (the small live blocks,
+    // contiguous so that one all-reduce covers them), sh 3M, then the blocks training never reads: colour 3, cov3D 6, conic 4
+    const int64_t widths[9] = {3, 3, 1, 3, 4, 3 * M, 3, 6, 4};
     int64_t offs[10]; offs[0] = 0;
     for (int i = 0; i < 9; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;   // keep 16-byte alignment
     torch::Tensor flat = torch::empty({offs[9]}, fopt);
     auto view = [&](int i, std::vector<int64_t> shape) { return flat.narrow(0, offs[i], widths[i] * P).view(shape); };
     torch::Tensor dL_dmeans3D = view(0, {P, 3}), dL_dmeans2D = view(1, {P, 3}), dL_dopacity = view(2, {P, 1}),
-                  dL_dsh = view(3, {P, M, 3}), dL_dscales = view(4, {P, 3}), dL_drotations = view(5, {P, 4}),
+                  dL_dscales = view(3, {P, 3}), dL_drotations = view(4, {P, 4}), dL_dsh = view(5, {P, M, 3}),
                   dL_dcolors = view(6, {P, 3}), dL_dcov3D = view(7, {P, 6}), dL_dconic = view(8, {P, 2, 2});
     if (P != 0) {
         auto bg = prep(background, dev, "bg"), m3 = prep(means3D, dev, "means3D"), col = prep(colors, dev, "colors_precomp"),
@@ -131,6 +133,12 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
         a.dL_dscale = dL_dscales.data_ptr<float>(); a.dL_drot = dL_drotations.data_ptr<float>();
         a.grad_scratch = reinterpret_cast<float*>(scratch.data_ptr());
         a.debug = debug; a.tile_row_begin = tile_row_begin; a.tile_row_end = tile_row_end;
+        if (drgb_block.has_value() && drgb_block->numel() > 0) {      // multi-view exchange block: campos (4) | dL_drgb (P,3)
+            TORCH_CHECK(drgb_block->scalar_type() == torch::kFloat32 && drgb_block->is_contiguous() && drgb_block->device() == dev &&
+                        drgb_block->numel() >= 4 + 3 * P, "drgb_block must be a contiguous float32 tensor of >= 4 + 3P elements on ", dev);
+            a.dL_drgb = drgb_block->data_ptr<float>() + 4;
+            a.skip_dL_dsh = skip_dsh ? 1 : 0;
+        }
         cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
         check(gsr_backward(&a, (void*)st));
     }
@@ -149,6 +157,19 @@ torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, tor
                                reinterpret_cast<unsigned char*>(present.data_ptr<bool>()), (void*)st));
     }
     return present;
+}
+
+// Fused SH-gradient exchange for multi-view training (gsr_multiview_sh_grad, include/gsr.h).  peer_ptrs are the device
+// addresses of every rank's exchange block (campos (4) | dL_drgb (P,3)) as mapped into THIS process (symmetric memory).
+void multiviewShGrad(const std::vector<int64_t>& peer_ptrs, const torch::Tensor& means3D, torch::Tensor& dL_dsh, const int degree) {
+    TORCH_CHECK(means3D.is_cuda() && dL_dsh.is_cuda() && dL_dsh.is_contiguous() && dL_dsh.dim() == 3, "bad tensors");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    std::vector<const float*> ptrs;
+    for (auto p : peer_ptrs) ptrs.push_back(reinterpret_cast<const float*>(p));
+    auto m3 = means3D.contiguous();
+    cudaStream_t st = c10::cuda::getCurrentCUDAStream(means3D.device().index()).stream();
+    check(gsr_multiview_sh_grad((int)means3D.size(0), degree, (int)dL_dsh.size(1), (int)ptrs.size(), ptrs.data(), m3.data_ptr<float>(),
+                                dL_dsh.data_ptr<float>(), (void*)st));
 }
 
 // introspection for the parity tests: (point_list, ranges, n_contrib, final_T, packed, tiles_touched, clamped) as tensors
@@ -180,7 +201,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("cov3D_precomp"), py::arg("viewmatrix"), py::arg("projmatrix"), py::arg("tan_fovx"), py::arg("tan_fovy"),
           py::arg("dL_dout_color"), py::arg("sh"), py::arg("degree"), py::arg("campos"), py::arg("geomBuffer"), py::arg("R"),
           py::arg("binningBuffer"), py::arg("imageBuffer"), py::arg("debug"), py::arg("tile_row_begin") = 0,
-          py::arg("tile_row_end") = 0);
+          py::arg("tile_row_end") = 0, py::arg("drgb_block") = py::none(), py::arg("skip_dsh") = false);
+    m.def("multiview_sh_grad", &multiviewShGrad);
     m.def("mark_visible", &markVisible);
     m.def("view_buffers", &viewBuffers);
 }

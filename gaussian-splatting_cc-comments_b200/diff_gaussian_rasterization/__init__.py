@@ -24,6 +24,17 @@ def cpu_deep_copy_tuple(input_tuple):
     return tuple(x.cpu().clone() if isinstance(x, torch.Tensor) else x for x in input_tuple)
 
 
+# Optional multi-view gradient exchange (one camera per GPU): an object with `.backward_extra(P, campos)` and
+# `.exchange(...)`, installed by gsr_multi_gpu.enable_multiview_training().  None = single-GPU behaviour, exactly the
+# reference's.
+_multiview = None
+
+
+def set_multiview_exchange(obj):
+    global _multiview
+    _multiview = obj
+
+
 def _band(raster_settings):
     """Optional tile-row band (begin, end) carried by settings that have one (multi-GPU render)."""
     return getattr(raster_settings, "tile_rows", None) or (0, 0)
@@ -71,6 +82,9 @@ class _RasterizeGaussians(torch.autograd.Function):
                 cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_out_color,
                 sh, rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
         band = _band(rs)
+        mv = _multiview if (_multiview is not None and sh.numel() > 0) else None
+        if mv is not None:   # publish masked dL/dRGB for the fused SH-gradient exchange instead of writing dL_dsh
+            band = (*band, mv.backward_extra(means3D.shape[0], rs.campos), True)
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:
@@ -83,6 +97,9 @@ class _RasterizeGaussians(torch.autograd.Function):
             grads = _C.rasterize_gaussians_backward(*args, *band)
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp,
          grad_sh, grad_scales, grad_rotations) = grads
+        if mv is not None:   # gradients come back summed over the ranks' views
+            mv.exchange(_C, means3D, rs.sh_degree, grad_sh,
+                        (grad_means3D, grad_means2D, grad_opacities, grad_scales, grad_rotations))
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities,
                 grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
 

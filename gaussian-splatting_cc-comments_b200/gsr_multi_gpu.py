@@ -191,3 +191,66 @@ def allreduce_radii(radii: torch.Tensor, group=None) -> torch.Tensor:
 def cameras_for_rank(n_views: int, rank: int, world: int) -> List[int]:
     """View c goes to rank c mod world: 8/4/2/1 views per GPU per step at 1/2/4/8 GPUs."""
     return [c for c in range(n_views) if c % world == rank]
+
+
+class MultiViewExchange:
+    """Fused gradient exchange for multi-view training, one camera per rank.
+
+    Per view the SH gradient is an outer product basis(dir_v) (x) dL/dRGB_v, so the 12*M bytes per Gaussian of
+    dL_dsh never cross the links.  Each rank's backward publishes 12 bytes per Gaussian (clamp-masked dL/dRGB)
+    plus its camera position in a peer-mapped (symmetric memory) block; after a device-side barrier ONE kernel
+    per rank (`gsr_multiview_sh_grad`) reads every rank's block over NVLink with peer loads and writes the
+    summed dL_dsh.  The 14 other live floats per Gaussian (means3D, means2D, opacity, scale, rotation) sit
+    contiguously in the gradient arena and are summed by one NCCL all-reduce that overlaps with that kernel.
+    Traffic per GPU at 8 ranks, P = 3 M: 252 MB of peer reads + a 168 MB all-reduce, instead of a 744 MB
+    all-reduce.
+    """
+
+    def __init__(self, capacity, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.group = group if group is not None else dist.group.WORLD
+        self.world = dist.get_world_size(self.group)
+        self.device = torch.device(device)
+        self._symm = symm_mem
+        self._alloc(int(capacity))
+
+    def _alloc(self, capacity):
+        self.capacity = capacity
+        self.block = self._symm.empty(4 + 3 * capacity, dtype=torch.float32, device=self.device)
+        self.block.zero_()
+        self.handle = self._symm.rendezvous(self.block, self.group)
+        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+
+    def backward_extra(self, P, campos):
+        """Called by the backward before its kernels: returns this rank's exchange block with campos written."""
+        if P > self.capacity:                     # densification grew the model: same P on every rank, so this is collective
+            self._alloc(int(P * 1.25) + 1024)
+        self.block[:3].copy_(campos.reshape(-1)[:3], non_blocking=True)
+        return self.block
+
+    def exchange(self, C, means3D, sh_degree, grad_sh, small_grads):
+        self.handle.barrier(channel=0)            # every rank's dL/dRGB and campos are in place
+        span = flat_span(small_grads)
+        works = []
+        if span is not None:
+            works.append(dist.all_reduce(span, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+        else:
+            works += [dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for g in small_grads]
+        C.multiview_sh_grad(self.peer_ptrs, means3D, grad_sh, int(sh_degree))      # overlaps with the all-reduce
+        for w in works:
+            w.wait()
+        self.handle.barrier(channel=1)            # nobody overwrites a block a peer is still reading
+
+
+def enable_multiview_training(capacity, device, group=None):
+    """Install the fused exchange: from now on `loss.backward()` through GaussianRasterizer returns gradients summed
+    over the ranks of `group` (each rank renders its own camera).  Collective.  Returns the exchange object."""
+    import diff_gaussian_rasterization as dgr
+    ex = MultiViewExchange(capacity, device, group)
+    dgr.set_multiview_exchange(ex)
+    return ex
+
+
+def disable_multiview_training():
+    import diff_gaussian_rasterization as dgr
+    dgr.set_multiview_exchange(None)

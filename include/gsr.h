@@ -108,6 +108,12 @@ typedef struct gsr_backward_args {
     float* grad_scratch;
     int debug;
     int tile_row_begin, tile_row_end;
+    /* Extension for multi-view training (one camera per GPU): when dL_drgb is not NULL the colour gradient
+     * with the SH clamp mask applied -- the (P,3) vector dL_dsh is an outer product of, see
+     * gsr_multiview_sh_grad -- is written there; with skip_dL_dsh != 0 the (P,M,3) dL_dsh block is then left
+     * untouched (it is produced by gsr_multiview_sh_grad from every rank's dL_drgb instead). */
+    float* dL_drgb;
+    int skip_dL_dsh;
 } gsr_backward_args;
 
 /* Bytes needed for gsr_backward_args.grad_scratch */
@@ -125,6 +131,17 @@ int gsr_forward(const gsr_forward_args* args,
 
 int gsr_backward(const gsr_backward_args* args, void* cuda_stream);
 
+/* Fused gradient exchange for the SH block in multi-view training (extension, no reference counterpart).
+ * Per view v the SH gradient is an outer product  dL_dsh_v[k] = basis_k(dir_v) * dL_drgb_v  (backward.cu:60-128),
+ * so instead of all-reducing 12*M bytes per Gaussian each rank publishes 12 bytes (dL_drgb_v) plus its camera
+ * position in peer-mapped memory and this ONE kernel reads every rank's block over NVLink (plain peer loads),
+ * rebuilds the basis per view and writes the summed dL_dsh (P,M,3), coefficients >= (D+1)^2 zeroed.
+ * peer_blocks[v] points to rank v's block: 4 floats (campos x,y,z,pad) followed by (P,3) floats dL_drgb.
+ * All pointers must be 16-byte aligned.  The caller orders it after every rank's gsr_backward (device barrier). */
+#define GSR_MAX_VIEWS 16
+int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* peer_blocks, const float* means3D,
+                          float* dL_dsh, void* cuda_stream);
+
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      unsigned char* present /* (P) bool out */, void* cuda_stream);
 
@@ -134,7 +151,7 @@ typedef struct gsr_buffer_view {
     const uint32_t* ranges;       /* (T,2) start/end into point_list per tile                   */
     const uint32_t* n_contrib;    /* (H*W)                                                      */
     const float* final_T;         /* (H*W)                                                      */
-    const float* packed;          /* (P,12) x,y,conic.xyz,opacity,r,g,b,ext_x,ext_y,power_thr   */
+    const float* packed;          /* (P,12) x,y,conic.xyz,power_thr,opacity,r,g,b,ext_x,ext_y   */
     const uint32_t* tiles_touched;/* (P)                                                        */
     const uint8_t* clamped;       /* (P) bit c set = colour channel c was clamped at 0          */
 } gsr_buffer_view;

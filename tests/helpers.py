@@ -115,7 +115,7 @@ def run_torch(mod, cam, scene, dL=None, bg=(0, 0, 0), use="sh", cov="sr", device
         pk = packed.cpu().numpy()
         out.update(point_list=pl.cpu().numpy().view(np.uint32), ranges=rg.cpu().numpy().view(np.uint32),
                    n_contrib=nc.cpu().numpy().view(np.uint32), final_T=ft.cpu().numpy(), packed=pk,
-                   means2D=pk[:, 0:2], conic_opacity=np.concatenate([pk[:, 2:5], pk[:, 5:6]], 1), rgb=pk[:, 6:9],
+                   means2D=pk[:, 0:2], conic_opacity=np.concatenate([pk[:, 2:5], pk[:, 6:7]], 1), rgb=pk[:, 7:10],
                    tiles_touched=tt.cpu().numpy().view(np.uint32), clamped_bits=cl.cpu().numpy())
     if dL is not None:
         color.backward(t(dL))

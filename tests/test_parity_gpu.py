@@ -226,3 +226,47 @@ def test_full_size_properties_c2(mod):
     if Hh.have_ref():
         ref = Hh.run_torch(Hh.ref_module(), cam, scene, dL, bg=(0.3, 0.5, 0.7), is_ref=True)
         assert_full_parity(mine, ref, exact_blend=True)
+
+
+def test_multiview_sh_gradient_kernel_equals_sum_of_single_view_gradients(mod):
+    """The fused SH-gradient exchange kernel (gsr_multiview_sh_grad), with the ranks emulated on ONE GPU: three cameras'
+    backward passes publish their masked dL/dRGB blocks (ordinary device tensors stand in for the peer-mapped blocks),
+    then one launch over all three blocks must equal the sum of the three ordinary dL_dsh -- and the other gradients
+    must be untouched by the extra output."""
+    import torch
+    import bench as B
+    P, W, H = 30000, 320, 200
+    cam0 = S.make_camera(W, H)
+    scene = S.make_scene(P, cam0, sh_degree=3, M=16, seed=4)
+    cams = [B.ring_camera(S, W, H, r) for r in (0, 3, 5)]
+    t = lambda a, rg=False: torch.tensor(np.asarray(a), dtype=torch.float32, device="cuda").requires_grad_(rg)
+    blocks, ref_sum, ref_small = [], None, None
+    for deg in (3, 1):
+        blocks, ref_sum = [], None
+        for ci, cam in enumerate(cams):
+            dL = t(S.upstream_grad(cam, seed=10 + ci))
+            st = mod.GaussianRasterizationSettings(H, W, cam["tanfovx"], cam["tanfovy"], t([0.1, 0.2, 0.3]), 1.0, t(cam["viewmatrix"]),
+                                                   t(cam["projmatrix"]), deg, t(cam["campos"]), False, False)
+            ins = dict(means3D=t(scene["means3D"]), sh=t(scene["shs"]), opac=t(scene["opacities"]), sc=t(scene["scales"]),
+                       rot=t(scene["rotations"]))
+            e = torch.Tensor([])
+            nr, color, radii, gb, bb, ib = mod._C.rasterize_gaussians(st.bg, ins["means3D"], e, ins["opac"], ins["sc"], ins["rot"], 1.0, e,
+                                                                      st.viewmatrix, st.projmatrix, st.tanfovx, st.tanfovy, H, W, ins["sh"],
+                                                                      deg, st.campos, False, False)
+            bargs = (st.bg, ins["means3D"], radii, e, ins["sc"], ins["rot"], 1.0, e, st.viewmatrix, st.projmatrix, st.tanfovx, st.tanfovy,
+                     dL, ins["sh"], deg, st.campos, gb, nr, bb, ib, False)
+            plain = mod._C.rasterize_gaussians_backward(*bargs)
+            blk = torch.zeros(4 + 3 * P, device="cuda")
+            blk[:3] = st.campos
+            fused = mod._C.rasterize_gaussians_backward(*bargs, 0, 0, blk, True)
+            for a, b, name in zip(plain, fused, ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")):
+                if name != "sh":
+                    assert Hh.rel_l2(b.cpu().numpy(), a.cpu().numpy()) <= 1e-5, name
+            blocks.append(blk)
+            ref_sum = plain[5].clone() if ref_sum is None else ref_sum + plain[5]
+        out = torch.full((P, 16, 3), 7.0, device="cuda")
+        mod._C.multiview_sh_grad([b.data_ptr() for b in blocks], t(scene["means3D"]), out, deg)
+        torch.cuda.synchronize()
+        K = (deg + 1) ** 2
+        assert Hh.rel_l2(out[:, :K].cpu().numpy(), ref_sum[:, :K].cpu().numpy()) <= 1e-5
+        assert float(out[:, K:].abs().max()) == 0.0 if K < 16 else True
