@@ -186,6 +186,7 @@ def run_gpu(args):
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
             os.environ["NCCL_DEBUG"] = "WARN"           # keep stdout to the one JSON line
+        os.environ.setdefault("TORCH_NCCL_HIGH_PRIORITY", "1")   # collectives overlap with compute kernels launched earlier
         torch.cuda.set_device(local)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     device = torch.device("cuda", local)
@@ -206,7 +207,7 @@ def run_gpu(args):
 
     # N > 1, this implementation: the fused exchange lives inside backward() (peer-mapped dL/dRGB blocks + one kernel
     # for the SH block, one NCCL all-reduce for the 14 small floats).  The reference arm all-reduces its tensors with NCCL.
-    fused = world > 1 and args.impl == "b200" and do_bwd and not args.plain_allreduce
+    fused = world > 1 and args.impl == "b200" and do_bwd and not args.plain_allreduce and not args.no_exchange
     if fused:
         MG.enable_multiview_training(P, device)
 
@@ -215,7 +216,7 @@ def run_gpu(args):
         color, radii = view.forward()
         if do_bwd:
             color.backward(dL)
-            if world > 1 and not fused:
+            if world > 1 and not fused and not args.no_exchange:
                 MG.allreduce_gradients(view.grads())
         return color
 
@@ -294,7 +295,7 @@ def run_gpu(args):
         if do_bwd:
             loss = (color * dL).sum()
             loss.backward()
-            if world > 1 and not fused:
+            if world > 1 and not fused and not args.no_exchange:
                 MG.allreduce_gradients(view.grads())
             loss_host.copy_(loss.detach().view(1), non_blocking=True)
         else:
@@ -434,6 +435,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-exchange", action="store_true", help="diagnostic: N > 1 without any gradient exchange (rank skew only)")
     ap.add_argument("--plain-allreduce", action="store_true", help="N > 1: one NCCL all-reduce of the whole gradient arena "
                     "instead of the fused SH-gradient exchange")
     args = ap.parse_args()

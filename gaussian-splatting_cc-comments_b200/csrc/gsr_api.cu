@@ -265,6 +265,11 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     }
     GSR_STAGE("render backward", st, a->debug);
 
+    const bool early_drgb = a->dL_drgb != nullptr && a->drgb_ready_event != nullptr;
+    if (early_drgb) {     // publish the 12 B/Gaussian the other ranks need first, so their copies overlap the rest of this call
+        launch_publish_drgb(P, acc, a->radii, a->shs ? geom.clamped : nullptr, a->dL_drgb, st);
+        GSR_CUDA(cudaEventRecord((cudaEvent_t)a->drgb_ready_event, st));
+    }
     PreprocessBwdArgs pb;
     pb.P = P; pb.D = a->D; pb.M = a->M;
     pb.means3D = a->means3D; pb.radii = a->radii; pb.shs = a->shs; pb.clamped = geom.clamped;
@@ -276,7 +281,7 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     pb.grad_acc = acc;
     pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dconic = a->dL_dconic; pb.dL_dopacity = a->dL_dopacity; pb.dL_dcolor = a->dL_dcolor;
     pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh; pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
-    pb.dL_drgb = a->dL_drgb; pb.skip_dsh = (a->dL_drgb != nullptr && a->skip_dL_dsh) ? 1 : 0;
+    pb.dL_drgb = early_drgb ? nullptr : a->dL_drgb; pb.skip_dsh = (a->dL_drgb != nullptr && a->skip_dL_dsh) ? 1 : 0;
     { StageTimer t(ST_PREPROCESS_BWD, st); launch_preprocess_backward(pb, st); }
     GSR_STAGE("preprocess backward", st, a->debug);
     return GSR_OK;

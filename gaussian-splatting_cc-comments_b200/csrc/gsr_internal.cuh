@@ -172,6 +172,9 @@ struct PreprocessBwdArgs {
     int skip_dsh;              // leave dL_dsh untouched
 };
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st);
+// masked colour gradient (P,3) from the blending accumulators: out = radii > 0 ? acc[6..8] with SH-clamped channels zeroed : 0
+void launch_publish_drgb(int P, const float* grad_acc, const int* radii, const uint8_t* clamped /* NULL: no mask */, float* out,
+                         cudaStream_t st);
 
 struct MultiviewShArgs {
     int P, D, M, n_views;

@@ -530,6 +530,29 @@ __global__ void __launch_bounds__(256) multiview_sh_grad_kernel_generic(Multivie
     for (int i = 0; i < 3 * a.M; i++) out[i] = (i < 3 * K) ? acc[i] : 0.f;
 }
 
+__global__ void __launch_bounds__(256) publish_drgb_kernel(int P, const float* __restrict__ grad_acc, const int* __restrict__ radii,
+                                                           const uint8_t* __restrict__ clamped, float* __restrict__ out) {
+    __shared__ float s[256 * 3];
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    float r = 0.f, g = 0.f, b = 0.f;
+    if (idx < P && radii[idx] > 0) {
+        const float4 q = reinterpret_cast<const float4*>(grad_acc + 12 * (size_t)idx)[1];    // acc[4..7]
+        const uint32_t cl = clamped ? clamped[idx] : 0u;
+        r = (cl & 1) ? 0.f : q.z; g = (cl & 2) ? 0.f : q.w; b = (cl & 4) ? 0.f : grad_acc[12 * (size_t)idx + 8];
+    }
+    s[3 * threadIdx.x] = r; s[3 * threadIdx.x + 1] = g; s[3 * threadIdx.x + 2] = b;
+    __syncthreads();
+    const size_t base = (size_t)blockIdx.x * 768;
+    const size_t n = (size_t)P * 3;
+    for (int i = threadIdx.x; i < 768; i += 256) if (base + i < n) out[base + i] = s[i];
+}
+
+void launch_publish_drgb(int P, const float* grad_acc, const int* radii, const uint8_t* clamped, float* out, cudaStream_t st) {
+    if (P <= 0) return;
+    publish_drgb_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, grad_acc, radii, clamped, out);
+    count_launch(1);
+}
+
 void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
     const int L = 3 * a.M;

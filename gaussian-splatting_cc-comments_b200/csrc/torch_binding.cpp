@@ -88,7 +88,7 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
                                const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
                                const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
                                const int tile_row_begin, const int tile_row_end,
-                               const c10::optional<torch::Tensor>& drgb_block, const bool skip_dsh) {
+                               const c10::optional<torch::Tensor>& drgb_block, const bool skip_dsh, const int64_t drgb_event) {
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
     const c10::cuda::CUDAGuard guard(means3D.device());
     const auto dev = means3D.device();
@@ -138,6 +138,7 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
                         drgb_block->numel() >= 4 + 3 * P, "drgb_block must be a contiguous float32 tensor of >= 4 + 3P elements on ", dev);
             a.dL_drgb = drgb_block->data_ptr<float>() + 4;
             a.skip_dL_dsh = skip_dsh ? 1 : 0;
+            a.drgb_ready_event = reinterpret_cast<void*>(drgb_event);      // cudaEvent_t (torch.cuda.Event.cuda_event) or 0
         }
         cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
         check(gsr_backward(&a, (void*)st));
@@ -201,7 +202,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("cov3D_precomp"), py::arg("viewmatrix"), py::arg("projmatrix"), py::arg("tan_fovx"), py::arg("tan_fovy"),
           py::arg("dL_dout_color"), py::arg("sh"), py::arg("degree"), py::arg("campos"), py::arg("geomBuffer"), py::arg("R"),
           py::arg("binningBuffer"), py::arg("imageBuffer"), py::arg("debug"), py::arg("tile_row_begin") = 0,
-          py::arg("tile_row_end") = 0, py::arg("drgb_block") = py::none(), py::arg("skip_dsh") = false);
+          py::arg("tile_row_end") = 0, py::arg("drgb_block") = py::none(), py::arg("skip_dsh") = false,
+          py::arg("drgb_event") = 0);
     m.def("multiview_sh_grad", &multiviewShGrad);
     m.def("mark_visible", &markVisible);
     m.def("view_buffers", &viewBuffers);

@@ -84,7 +84,7 @@ class _RasterizeGaussians(torch.autograd.Function):
         band = _band(rs)
         mv = _multiview if (_multiview is not None and sh.numel() > 0) else None
         if mv is not None:   # publish masked dL/dRGB for the fused SH-gradient exchange instead of writing dL_dsh
-            band = (*band, mv.backward_extra(means3D.shape[0], rs.campos), True)
+            band = (*band, *mv.backward_extra(means3D.shape[0], rs.campos))
         if rs.debug:
             cpu_args = cpu_deep_copy_tuple(args)
             try:

@@ -194,59 +194,100 @@ def cameras_for_rank(n_views: int, rank: int, world: int) -> List[int]:
 
 
 class MultiViewExchange:
-    """Fused gradient exchange for multi-view training, one camera per rank.
+    """Gradient exchange for multi-view training, one camera per rank.
 
     Per view the SH gradient is an outer product basis(dir_v) (x) dL/dRGB_v, so the 12*M bytes per Gaussian of
     dL_dsh never cross the links.  Each rank's backward publishes 12 bytes per Gaussian (clamp-masked dL/dRGB)
-    plus its camera position in a peer-mapped (symmetric memory) block; after a device-side barrier ONE kernel
-    per rank (`gsr_multiview_sh_grad`) reads every rank's block over NVLink with peer loads and writes the
-    summed dL_dsh.  The 14 other live floats per Gaussian (means3D, means2D, opacity, scale, rotation) sit
-    contiguously in the gradient arena and are summed by one NCCL all-reduce that overlaps with that kernel.
-    Traffic per GPU at 8 ranks, P = 3 M: 252 MB of peer reads + a 168 MB all-reduce, instead of a 744 MB
+    plus its camera position in a peer-mapped (symmetric memory) block as soon as the blending backward is done
+    and records an event.  From there two things run side by side:
+      * side stream: device barrier, then the 7 peers' blocks are pulled over NVLink by the copy engines (no SMs)
+        into local staging, second barrier (blocks may be overwritten again);
+      * main stream: the per-Gaussian backward (HBM/SM bound), which overlaps with those copies.
+    Then ONE kernel (`gsr_multiview_sh_grad`) rebuilds every view's SH basis and writes the summed dL_dsh, while
+    the 14 other live floats per Gaussian (means3D, means2D, opacity, scale, rotation -- contiguous in the
+    gradient arena) are summed by one NCCL all-reduce that overlaps with that kernel (NVLink vs SM/HBM).
+    NVLink traffic per GPU at 8 ranks, P = 3 M: 252 MB of peer copies + a 168 MB all-reduce, instead of a 744 MB
     all-reduce.
     """
 
-    def __init__(self, capacity, device, group=None):
+    def __init__(self, capacity, device, group=None, mode=None):
+        import os
         import torch.distributed._symmetric_memory as symm_mem
         self.group = group if group is not None else dist.group.WORLD
         self.world = dist.get_world_size(self.group)
+        self.rank = dist.get_rank(self.group)
         self.device = torch.device(device)
+        # how the 12 B/Gaussian blocks travel: "allgather" (default) = NCCL all-gather into local staging, then the SH
+        # kernel on local data; "peer" = plain peer loads inside the SH kernel (symmetric memory).  Measured on 8 B200:
+        # 5.18 vs 5.36 ms per step (profiles/r01_multigpu_c5.md) -- the all-gather goes through NVLS.
+        self.mode = mode or os.environ.get("GSR_MULTIVIEW_MODE", "allgather")
         self._symm = symm_mem
+        # high priority: the exchange's few CTAs must be dispatched WHILE the per-Gaussian backward (tens of thousands of
+        # short blocks, launched earlier) is running, not after it.  For the NCCL part set TORCH_NCCL_HIGH_PRIORITY=1
+        # before init_process_group (bench.py does).
+        self.side = torch.cuda.Stream(device=self.device, priority=-1)
+        self.ev_drgb = torch.cuda.Event()
+        self.ev_done = torch.cuda.Event()
+        with torch.cuda.device(self.device):
+            self.ev_drgb.record()                 # torch creates the cudaEvent lazily; the C ABI needs the handle
+            self.ev_done.record()
         self._alloc(int(capacity))
 
     def _alloc(self, capacity):
         self.capacity = capacity
-        self.block = self._symm.empty(4 + 3 * capacity, dtype=torch.float32, device=self.device)
-        self.block.zero_()
-        self.handle = self._symm.rendezvous(self.block, self.group)
-        self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+        n = 4 + 3 * capacity
+        if self.mode == "allgather":
+            self.block = torch.zeros(n, dtype=torch.float32, device=self.device)
+            self.stage = torch.zeros(self.world * n, dtype=torch.float32, device=self.device)
+            self.handle, self.peer_ptrs = None, None
+        else:
+            self.block = self._symm.empty(n, dtype=torch.float32, device=self.device)
+            self.block.zero_()
+            self.handle = self._symm.rendezvous(self.block, self.group)
+            self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
+            self.stage = None
 
     def backward_extra(self, P, campos):
-        """Called by the backward before its kernels: returns this rank's exchange block with campos written."""
+        """Called by the backward before its kernels: (exchange block with campos written, skip_dsh, event handle)."""
         if P > self.capacity:                     # densification grew the model: same P on every rank, so this is collective
             self._alloc(int(P * 1.25) + 1024)
         self.block[:3].copy_(campos.reshape(-1)[:3], non_blocking=True)
-        return self.block
+        return self.block, True, int(self.ev_drgb.cuda_event)
 
     def exchange(self, C, means3D, sh_degree, grad_sh, small_grads):
-        self.handle.barrier(channel=0)            # every rank's dL/dRGB and campos are in place
-        span = flat_span(small_grads)
-        works = []
+        P = means3D.shape[0]
+        n = 4 + 3 * P
+        main = torch.cuda.current_stream(self.device)
+        # side stream: starts as soon as dL/dRGB is published (event recorded by gsr_backward right after the blending
+        # backward), i.e. it runs beside the per-Gaussian backward that the main stream is still executing
+        self.side.wait_event(self.ev_drgb)
+        with torch.cuda.stream(self.side):
+            if self.mode == "allgather":
+                out = self.stage[: self.world * n]
+                dist.all_gather_into_tensor(out, self.block[:n], group=self.group)
+                ptrs = [out[r * n:].data_ptr() for r in range(self.world)]
+                C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
+            else:
+                self.handle.barrier(channel=0)    # every rank's dL/dRGB and campos are in place
+                # start with the next rank's block so that the ranks do not all pull from the same GPU at once
+                ptrs = [self.peer_ptrs[(self.rank + 1 + i) % self.world] for i in range(self.world)]
+                C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
+                self.handle.barrier(channel=1)    # nobody overwrites a block a peer is still reading
+            self.ev_done.record(self.side)
+        span = flat_span(small_grads)             # main stream: ordered after the per-Gaussian backward
         if span is not None:
-            works.append(dist.all_reduce(span, op=dist.ReduceOp.SUM, group=self.group, async_op=True))
+            dist.all_reduce(span, op=dist.ReduceOp.SUM, group=self.group)
         else:
-            works += [dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group, async_op=True) for g in small_grads]
-        C.multiview_sh_grad(self.peer_ptrs, means3D, grad_sh, int(sh_degree))      # overlaps with the all-reduce
-        for w in works:
-            w.wait()
-        self.handle.barrier(channel=1)            # nobody overwrites a block a peer is still reading
+            for g in small_grads:
+                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
+        main.wait_event(self.ev_done)
 
 
-def enable_multiview_training(capacity, device, group=None):
+def enable_multiview_training(capacity, device, group=None, mode=None):
     """Install the fused exchange: from now on `loss.backward()` through GaussianRasterizer returns gradients summed
     over the ranks of `group` (each rank renders its own camera).  Collective.  Returns the exchange object."""
     import diff_gaussian_rasterization as dgr
-    ex = MultiViewExchange(capacity, device, group)
+    ex = MultiViewExchange(capacity, device, group, mode)
     dgr.set_multiview_exchange(ex)
     return ex
 

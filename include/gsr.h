@@ -114,6 +114,10 @@ typedef struct gsr_backward_args {
      * untouched (it is produced by gsr_multiview_sh_grad from every rank's dL_drgb instead). */
     float* dL_drgb;
     int skip_dL_dsh;
+    /* Optional cudaEvent_t recorded on the stream as soon as dL_drgb is complete -- right after the blending
+     * backward, BEFORE the per-Gaussian backward runs -- so that the exchange of dL_drgb between ranks can
+     * overlap with the rest of this call.  NULL = no event. */
+    void* drgb_ready_event;
 } gsr_backward_args;
 
 /* Bytes needed for gsr_backward_args.grad_scratch */

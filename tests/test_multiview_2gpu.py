@@ -40,10 +40,13 @@ def _worker(rank, world, port, q):
         for c, dL in zip(cams, dLs):
             g = Hh.run_torch(mod, c, scene, dL, bg=(0.1, 0.2, 0.3), device=dev)["grads"]
             expect = g if expect is None else {k: (expect[k] + g[k] if g[k] is not None else None) for k in g}
-        MG.enable_multiview_training(P, dev)
-        got = Hh.run_torch(mod, cams[rank], scene, dLs[rank], bg=(0.1, 0.2, 0.3), device=dev)["grads"]
-        MG.disable_multiview_training()
-        errs = {k: float(Hh.rel_l2(got[k], expect[k])) for k in ("means3D", "means2D", "shs", "opacities", "scales", "rotations")}
+        errs = {}
+        for mode in ("allgather", "peer"):
+            MG.enable_multiview_training(P, dev, mode=mode)
+            got = Hh.run_torch(mod, cams[rank], scene, dLs[rank], bg=(0.1, 0.2, 0.3), device=dev)["grads"]
+            MG.disable_multiview_training()
+            errs.update({mode + "/" + k: float(Hh.rel_l2(got[k], expect[k]))
+                         for k in ("means3D", "means2D", "shs", "opacities", "scales", "rotations")})
         q.put((rank, errs))
     finally:
         dist.destroy_process_group()

@@ -258,7 +258,10 @@ def test_multiview_sh_gradient_kernel_equals_sum_of_single_view_gradients(mod):
             plain = mod._C.rasterize_gaussians_backward(*bargs)
             blk = torch.zeros(4 + 3 * P, device="cuda")
             blk[:3] = st.campos
-            fused = mod._C.rasterize_gaussians_backward(*bargs, 0, 0, blk, True)
+            ev = torch.cuda.Event()
+            ev.record()                                   # forces the cudaEvent to exist
+            # odd cameras take the early-publish path (dL/dRGB written right after the blending backward + event record)
+            fused = mod._C.rasterize_gaussians_backward(*bargs, 0, 0, blk, True, int(ev.cuda_event) if ci % 2 else 0)
             for a, b, name in zip(plain, fused, ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")):
                 if name != "sh":
                     assert Hh.rel_l2(b.cpu().numpy(), a.cpu().numpy()) <= 1e-5, name
