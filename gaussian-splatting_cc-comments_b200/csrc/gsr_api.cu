@@ -278,7 +278,7 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     pb.W = W; pb.H = H; pb.tan_fovx = a->tan_fovx; pb.tan_fovy = a->tan_fovy;
     pb.focal_y = H / (2.0f * a->tan_fovy);     // rasterizer_impl.cu:459-460
     pb.focal_x = W / (2.0f * a->tan_fovx);
-    pb.grad_acc = acc;
+    pb.grad_acc = acc; pb.packed = geom.packed;
     pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dconic = a->dL_dconic; pb.dL_dopacity = a->dL_dopacity; pb.dL_dcolor = a->dL_dcolor;
     pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh; pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
     pb.dL_drgb = early_drgb ? nullptr : a->dL_drgb; pb.skip_dsh = (a->dL_drgb != nullptr && a->skip_dL_dsh) ? 1 : 0;

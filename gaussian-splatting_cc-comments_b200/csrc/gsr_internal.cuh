@@ -165,7 +165,8 @@ struct PreprocessBwdArgs {
     const float* scales; const float* rotations; float scale_modifier; const float* cov3D_precomp;
     Camera cam;
     int W, H; float tan_fovx, tan_fovy, focal_x, focal_y;
-    const float* grad_acc;     // (P,12)
+    const float* grad_acc;     // (P,12): sum w dx, w dy, w dx dx, w dx dy, w dy dy, dL_dopacity, dL_dcolour[3]
+    const float4* packed;      // the forward's records (conic)
     float* dL_dmean2D; float* dL_dconic; float* dL_dopacity; float* dL_dcolor;
     float* dL_dmean3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;
     float* dL_drgb;            // optional (P,3): clamp-masked colour gradient (multi-view exchange)

@@ -194,7 +194,15 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
     float* g = o.g; float* dmean = o.dmean; float* dcov = o.dcov;
     const float4* ga = reinterpret_cast<const float4*>(a.grad_acc + 12 * (size_t)idx);
     const float4 g0 = ga[0], g1 = ga[1];
-    g[0] = g0.x; g[1] = g0.y; g[2] = g0.z; g[3] = g0.w; g[4] = g1.x; g[5] = g1.y; g[6] = g1.z; g[7] = g1.w;
+    {   // the blending backward reduced moments (gsr_render_bwd.cu); combine them with this Gaussian's conic:
+        // dL_dmean2D = -(conic * [sum w dx, sum w dy]) * (W/2, H/2), dL_dconic = -1/2 [sum w dx dx, sum w dx dy, sum w dy dy]
+        const float4 pa = __ldg(a.packed + 3 * (size_t)idx);          // x, y, conic.x, conic.y
+        const float conz = __ldg(reinterpret_cast<const float*>(a.packed + 3 * (size_t)idx + 1));
+        g[0] = (-g0.x * pa.z - g0.y * pa.w) * (0.5f * a.W);           // backward.cu:587
+        g[1] = (-g0.y * conz - g0.x * pa.w) * (0.5f * a.H);           // backward.cu:588
+        g[2] = -0.5f * g0.z; g[3] = -0.5f * g0.w; g[4] = -0.5f * g1.x;
+    }
+    g[5] = g1.y; g[6] = g1.z; g[7] = g1.w;
     g[8] = a.grad_acc[12 * (size_t)idx + 8];
     const float mx = __ldg(a.means3D + i3), my = __ldg(a.means3D + i3 + 1), mz = __ldg(a.means3D + i3 + 2);
     float c3[6];

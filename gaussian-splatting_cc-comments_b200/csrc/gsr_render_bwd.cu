@@ -66,7 +66,6 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
     float ar0 = 0.f, ar1 = 0.f, ar2 = 0.f;       // accum_rec
     float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;       // last_color
     float last_alpha = 0.f;
-    const float ddelx_dx = 0.5f * W, ddely_dy = 0.5f * H;
 
     // block / warp maxima of the last contributor: nothing behind them has a gradient
     const int wmax = (int)__reduce_max_sync(0xffffffffu, (uint32_t)last_contributor);
@@ -132,7 +131,8 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
                             contrib = true;
                             const float2 gb = lds64<BOFF_C>(ja);   // g, b
                             const float one_m_alpha = 1.0f - alpha;
-                            const float inv = __frcp_rn(one_m_alpha);
+                            float inv;                                     // 1 - alpha >= 0.01: MUFU.RCP (1 ulp) is enough here
+                            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(one_m_alpha));
                             T = T * inv;                                   // backward.cu:534
                             const float dchannel_dcolor = alpha * T;
                             // backward.cu:542-562
@@ -147,15 +147,17 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
                             dL_dalpha *= T;
                             last_alpha = alpha;
                             dL_dalpha += (-T_final * inv) * bg_dot_dpixel;  // backward.cu:571-574
-                            const float dL_dG = b.z * dL_dalpha;
-                            const float gdx = G * dx, gdy = G * dy;
-                            const float dG_ddelx = -gdx * a.z - gdy * a.w;
-                            const float dG_ddely = -gdy * b.x - gdx * a.w;
-                            v[0] = dL_dG * dG_ddelx * ddelx_dx;             // backward.cu:587-598
-                            v[1] = dL_dG * dG_ddely * ddely_dy;
-                            v[2] = -0.5f * gdx * dx * dL_dG;
-                            v[3] = -0.5f * gdx * dy * dL_dG;
-                            v[4] = -0.5f * gdy * dy * dL_dG;
+                            // backward.cu:577-598.  All five geometric gradients are linear in the moments
+                            // sum(w), sum(w dx), sum(w dy), sum(w dx dx), sum(w dx dy), sum(w dy dy) with
+                            // w = dL_dG * G; only the moments are reduced here, the per-Gaussian combinations with
+                            // the conic (constant over the sum) are applied once in the preprocess backward.
+                            const float w = (b.z * dL_dalpha) * G;
+                            const float wx = w * dx, wy = w * dy;
+                            v[0] = wx;
+                            v[1] = wy;
+                            v[2] = wx * dx;
+                            v[3] = wx * dy;
+                            v[4] = wy * dy;
                             v[5] = G * dL_dalpha;
                         }
                     }
