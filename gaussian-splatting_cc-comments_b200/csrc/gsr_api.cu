@@ -176,10 +176,8 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     // depth order of the Gaussians: 4 stable 8-bit passes, result back in keys[0]/vals[0]
     {
         StageTimer t(ST_DEPTH_SORT, st);
-        for (int pass = 0; pass < 4; pass++) {
-            const int s = pass & 1;
-            radix_pass_u32(geom.keys[s], geom.vals[s], geom.keys[s ^ 1], geom.vals[s ^ 1], P, 8 * pass, 8, geom.table, geom.scan_tmp, st);
-        }
+        const int shifts[4] = {0, 8, 16, 24}, bits[4] = {8, 8, 8, 8};
+        radix_sort_u32(geom.keys, geom.vals, 0, P, 4, shifts, bits, geom.table, st);
     }
     GSR_STAGE("depth sort", st, a->debug);
     {
@@ -212,12 +210,13 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
         StageTimer t(ST_TILE_SORT, st);
         // digits of equal width (13 tile bits -> 7 + 6): fewer bins per pass = longer contiguous runs per block
         const int per = npass ? (tile_bits + npass - 1) / npass : 0;
+        int shifts[4] = {0, 0, 0, 0}, bits[4] = {0, 0, 0, 0};
         for (int pass = 0, shift = 0; pass < npass; pass++) {
-            const int bits = (tile_bits - shift) < per ? (tile_bits - shift) : per;
-            radix_pass_u32(bin.keys[s], bin.vals[s], bin.keys[s ^ 1], bin.vals[s ^ 1], R, shift, bits, bin.table, bin.scan_tmp, st);
-            shift += bits;
-            s ^= 1;
+            bits[pass] = (tile_bits - shift) < per ? (tile_bits - shift) : per;
+            shifts[pass] = shift;
+            shift += bits[pass];
         }
+        radix_sort_u32(bin.keys, bin.vals, s, R, npass, shifts, bits, bin.table, st);
     }
     GSR_STAGE("tile sort", st, a->debug);
     { StageTimer t(ST_RANGES, st); launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st); }
@@ -225,7 +224,7 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     {
         StageTimer t(ST_RENDER, st);
         launch_render_forward(grid_x, row_begin, row_end, img.ranges, bin.vals[0], W, H, geom.packed, a->background,
-                              a->out_color, img.final_T, img.n_contrib, st);
+                              a->out_color, img.final_T, img.n_contrib, bin.warp_mask, st);
     }
     GSR_STAGE("render", st, a->debug);
     *num_rendered = (int)R;
@@ -261,7 +260,7 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     if (a->R > 0) {
         StageTimer t(ST_RENDER_BWD, st);
         launch_render_backward(grid_x, row_begin, row_end, img.ranges, bin.vals[0], W, H, geom.packed, a->background,
-                               img.final_T, img.n_contrib, a->dL_dpix, acc, st);
+                               img.final_T, img.n_contrib, a->dL_dpix, acc, bin.warp_mask, st);
     }
     GSR_STAGE("render backward", st, a->debug);
 

@@ -151,13 +151,16 @@ void scan_exclusive_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t* t
 // equal digits find each other with match.any; the lowest such lane bumps the warp's private digit counter.
 constexpr uint32_t LB_AGG = 1u << 30, LB_PREFIX = 2u << 30, LB_MASK = (1u << 30) - 1u;
 
-__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, int shift, int bits,
+struct RsPasses { int n; int shift[4]; int bits[4]; };
+
+// Digit histograms of ALL passes of one sort in a single read of the keys (the key set does not change between
+// passes, only its order).  ghist[p*256 + d] += count of keys whose pass-p digit is d.
+__global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, RsPasses ps,
                                                              uint32_t* __restrict__ ghist) {
-    __shared__ uint32_t s_hist[8 * RS_BINS];
-    const uint32_t mask = (1u << bits) - 1u;
+    extern __shared__ uint32_t s_hist[];          // [8 warps][ps.n][RS_BINS]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t* wh = s_hist + w * RS_BINS;
-    for (int i = lane; i < RS_BINS; i += 32) wh[i] = 0;
+    uint32_t* wh = s_hist + w * ps.n * RS_BINS;
+    for (int i = lane; i < ps.n * RS_BINS; i += 32) wh[i] = 0;
     __syncwarp();
     const size_t n4 = n >> 2;
     const uint4* k4 = reinterpret_cast<const uint4*>(keys);
@@ -166,24 +169,33 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __r
         const size_t i = base + lane;
         const bool ok = i < n4;
         const uint4 q = ok ? __ldg(k4 + i) : make_uint4(0, 0, 0, 0);
-        const uint32_t d[4] = {(q.x >> shift) & mask, (q.y >> shift) & mask, (q.z >> shift) & mask, (q.w >> shift) & mask};
+        const uint32_t kk[4] = {q.x, q.y, q.z, q.w};
+        for (int p = 0; p < ps.n; p++) {
+            const uint32_t mask = (1u << ps.bits[p]) - 1u;
+            uint32_t* hp = wh + p * RS_BINS;
 #pragma unroll
-        for (int j = 0; j < 4; j++) {
-            // whole warp on one digit (high bytes of depth keys): one add instead of a 32-way same-address atomic
-            const uint32_t dj = ok ? d[j] : 0xFFFFFFFFu;
-            const uint32_t d0 = __shfl_sync(0xffffffffu, dj, 0);
-            if (__all_sync(0xffffffffu, dj == d0)) { if (lane == 0) wh[d0] += 32; }
-            else if (ok) atomicAdd(&wh[dj], 1u);
-            __syncwarp();
+            for (int j = 0; j < 4; j++) {
+                // whole warp on one digit (high bytes of depth keys): one add instead of a 32-way same-address atomic
+                const uint32_t dj = ok ? ((kk[j] >> ps.shift[p]) & mask) : 0xFFFFFFFFu;
+                const uint32_t d0 = __shfl_sync(0xffffffffu, dj, 0);
+                if (__all_sync(0xffffffffu, dj == d0)) { if (lane == 0) hp[d0] += 32; }
+                else if (ok) atomicAdd(&hp[dj], 1u);
+                __syncwarp();
+            }
         }
     }
-    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) atomicAdd(&wh[(keys[4 * n4 + threadIdx.x] >> shift) & mask], 1u);
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+        const uint32_t key = keys[4 * n4 + threadIdx.x];
+        for (int p = 0; p < ps.n; p++) atomicAdd(&wh[p * RS_BINS + ((key >> ps.shift[p]) & ((1u << ps.bits[p]) - 1u))], 1u);
+    }
     __syncthreads();
     const int d = threadIdx.x;   // RS_THREADS == RS_BINS
-    uint32_t c = 0;
+    for (int p = 0; p < ps.n; p++) {
+        uint32_t c = 0;
 #pragma unroll
-    for (int ww = 0; ww < 8; ww++) c += s_hist[ww * RS_BINS + d];
-    if (c) atomicAdd(&ghist[d], c);
+        for (int ww = 0; ww < 8; ww++) c += s_hist[(ww * ps.n + p) * RS_BINS + d];
+        if (c) atomicAdd(&ghist[p * RS_BINS + d], c);
+    }
 }
 
 __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
@@ -289,17 +301,26 @@ __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __
     }
 }
 
-// `table` holds [0,256) the pass's global digit histogram, [256] the ticket counter, [512, 512 + 256*tiles) the look-back table
-void radix_pass_u32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, size_t n,
-                    int shift, int bits, uint32_t* table, uint32_t* scan_tmp, cudaStream_t st) {
-    (void)scan_tmp;
-    if (n == 0) return;
+// Stable LSD sort of n (key, value) pairs on the given digit passes; input in keys[s0]/vals[s0], the result ends
+// in keys[s0 ^ (npass & 1)].  `table` (rs_table_words(n) words) holds the digit histograms of all passes
+// [p*256, p*256+256), the ticket counters [1024 + p] and one look-back table per pass from word 1280.
+void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, size_t n, int npass, const int* shifts,
+                    const int* bits, uint32_t* table, cudaStream_t st) {
+    if (n == 0 || npass <= 0) return;
     const unsigned nb = (unsigned)rs_blocks(n);
-    cudaMemsetAsync(table, 0, (512 + (size_t)nb * RS_BINS) * sizeof(uint32_t), st);
+    cudaMemsetAsync(table, 0, (1280 + (size_t)npass * nb * RS_BINS) * sizeof(uint32_t), st);
+    RsPasses ps;
+    ps.n = npass;
+    for (int p = 0; p < 4; p++) { ps.shift[p] = p < npass ? shifts[p] : 0; ps.bits[p] = p < npass ? bits[p] : 1; }
     const unsigned hb = (unsigned)min((size_t)(148 * 8), (n / 4 + RS_THREADS - 1) / RS_THREADS + 1);
-    rs_hist_kernel<<<hb, RS_THREADS, 0, st>>>(kin, n, shift, bits, table);
-    rs_sweep_kernel<<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, table, table + 256, table + 512);
-    count_launch(2);
+    rs_hist_kernel<<<hb, RS_THREADS, (size_t)8 * npass * RS_BINS * sizeof(uint32_t), st>>>(keys[s0], n, ps, table);
+    int s = s0;
+    for (int p = 0; p < npass; p++) {
+        rs_sweep_kernel<<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
+                                                   table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
+        s ^= 1;
+    }
+    count_launch(1 + npass);
 }
 
 // ------------------------------------------------------------------------------------------------

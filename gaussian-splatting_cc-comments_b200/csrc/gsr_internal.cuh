@@ -45,6 +45,7 @@ constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // 4096
 
 static inline size_t rs_blocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
+static inline size_t rs_table_words(size_t n) { return 1280 + 4 * rs_blocks(n) * RS_BINS; }   // see radix_sort_u32
 static inline size_t scan_blocks(size_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
 
 struct GeomState {
@@ -69,7 +70,7 @@ struct GeomState {
         g.vals[0] = c.take<uint32_t>(P); g.vals[1] = c.take<uint32_t>(P);
         g.tt_sorted = c.take<uint32_t>(P);
         g.offsets = c.take<uint32_t>(P);
-        size_t tbl = rs_blocks(P) * RS_BINS + 512;
+        size_t tbl = rs_table_words(P);
         g.table = c.take<uint32_t>(tbl);
         size_t big = tbl > P ? tbl : P;
         g.scan_tmp = c.take<uint32_t>(scan_blocks(big) + 1);
@@ -85,14 +86,16 @@ struct BinState {
     uint32_t* keys[2];         // R each: tile ids, ping-pong
     uint32_t* table;           // rs_blocks(R) * RS_BINS + 512
     uint32_t* scan_tmp;
+    uint8_t* warp_mask;        // R: bit w = warp w of the instance's tile blended it in the forward (backward's cull)
     size_t bytes;
     static BinState carve(char* base, size_t R) {
         BinState b; Carver c(base);
         b.vals[0] = c.take<uint32_t>(R); b.vals[1] = c.take<uint32_t>(R);
         b.keys[0] = c.take<uint32_t>(R); b.keys[1] = c.take<uint32_t>(R);
-        size_t tbl = rs_blocks(R) * RS_BINS + 512;
+        size_t tbl = rs_table_words(R);
         b.table = c.take<uint32_t>(tbl);
         b.scan_tmp = c.take<uint32_t>(scan_blocks(tbl) + 1);
+        b.warp_mask = c.take<uint8_t>(R);
         b.bytes = align_up(c.off, 256) + 256;
         return b;
     }
@@ -138,9 +141,9 @@ void launch_mark_visible(int P, const float* means, const float* view, unsigned 
 // if total != nullptr the grand total is written there.
 void scan_exclusive_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t* tmp, uint32_t* total, cudaStream_t st);
 
-// one stable LSD pass on `bits` (<= 8) key bits starting at `shift`
-void radix_pass_u32(const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout, size_t n,
-                    int shift, int bits, uint32_t* table, uint32_t* scan_tmp, cudaStream_t st);
+// stable LSD radix sort on up to 4 digit passes (bits[p] <= 8 key bits starting at shifts[p]); see gsr_binning.cu
+void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, size_t n, int npass, const int* shifts,
+                    const int* bits, uint32_t* table, cudaStream_t st);
 
 void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, size_t n, cudaStream_t st);
 
@@ -152,12 +155,12 @@ void launch_tile_ranges(size_t R, const uint32_t* sorted_tile_keys, uint2* range
 
 void launch_render_forward(int grid_x, int row_begin, int row_end, const uint2* ranges, const uint32_t* point_list,
                            int W, int H, const float4* packed, const float* bg, float* out_color,
-                           float* final_T, uint32_t* n_contrib, cudaStream_t st);
+                           float* final_T, uint32_t* n_contrib, uint8_t* warp_mask, cudaStream_t st);
 
 void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2* ranges, const uint32_t* point_list,
                             int W, int H, const float4* packed, const float* bg, const float* final_T,
                             const uint32_t* n_contrib, const float* dL_dpix, float* grad_acc /* (P,12) */,
-                            cudaStream_t st);
+                            const uint8_t* warp_mask, cudaStream_t st);
 
 struct PreprocessBwdArgs {
     int P, D, M;

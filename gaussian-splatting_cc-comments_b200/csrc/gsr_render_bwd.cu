@@ -20,6 +20,7 @@ namespace gsr {
 
 constexpr int RBB = GSR_TILE_PIX;
 constexpr int BOFF_B = RBB * 16, BOFF_C = 2 * RBB * 16, BOFF_ID = 3 * RBB * 16;   // byte offsets of the b / c / id planes
+constexpr int BOFF_MB = BOFF_ID + RBB * 4;                                         // per-instance warp masks (1 byte each)
 
 template <int N>
 __device__ __forceinline__ void reduce_scatter_step(float* v, int bit, bool upper) {
@@ -35,8 +36,9 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
                                                          int W, int H, int grid_x, int row_begin,
                                                          const float4* __restrict__ packed, const float* __restrict__ bg,
                                                          const float* __restrict__ final_Ts, const uint32_t* __restrict__ n_contrib,
-                                                         const float* __restrict__ dL_dpixels, float* __restrict__ grad_acc) {
-    __shared__ __align__(16) float4 s_rec[3 * RBB + RBB / 4];    // planes a | b | c of the staged records, then their ids
+                                                         const float* __restrict__ dL_dpixels, float* __restrict__ grad_acc,
+                                                         const uint8_t* __restrict__ warp_mask) {
+    __shared__ __align__(16) float4 s_rec[3 * RBB + RBB / 4 + RBB / 16];    // planes a | b | c of the staged records, ids, warp masks
     __shared__ uint32_t s_max[8];
     const uint32_t sb = smem_addr(s_rec);
 
@@ -47,7 +49,6 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
     const int pix_x = bx0 + (lane & 7), pix_y = by0 + (lane >> 3);
     const bool inside = pix_x < W && pix_y < H;
     const float pixfx = (float)pix_x, pixfy = (float)pix_y;
-    const float fx0 = (float)bx0, fx1 = (float)(bx0 + 7), fy0 = (float)by0, fy1 = (float)(by0 + 3);
     const size_t pix_id = (size_t)pix_y * W + pix_x;
     const size_t HW = (size_t)H * W;
 
@@ -89,6 +90,7 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
             sts128<BOFF_B>(my_slot, rb);
             sts128<BOFF_C>(my_slot, rc);
             sts32u<BOFF_ID>(sb + threadIdx.x * 4, id);
+            sts8u<BOFF_MB>(sb + threadIdx.x, warp_mask[range.x + mypos]);
         }
         __syncthreads();
         const int count = min(RBB, first_pos + 1);
@@ -96,15 +98,10 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
         for (int cbase = 0; cbase < count; cbase += 32) {
             // lane l tests staged Gaussian cbase + 31 - l: the next one to replay is the highest set ballot bit
             const int jj = cbase + 31 - lane;
+            // the forward recorded, per instance, which warps of the tile blended it (gsr_render.cu): exactly the
+            // (Gaussian, warp) pairs with a gradient, so no geometric test and no empty replays here
             bool hit = false;
-            if (jj < count && first_pos - jj < wmax) {
-                const uint32_t ja = sb + (uint32_t)jj * 16;
-                const float2 xy = lds64<0>(ja);
-                const float2 ext = lds64<BOFF_C + 8>(ja);
-                const float ddx = fmaxf(fmaxf(fx0 - xy.x, xy.x - fx1), 0.0f);
-                const float ddy = fmaxf(fmaxf(fy0 - xy.y, xy.y - fy1), 0.0f);
-                hit = (ddx <= ext.x) && (ddy <= ext.y);
-            }
+            if (jj < count && first_pos - jj < wmax) hit = (lds8u<BOFF_MB>(sb + (uint32_t)jj) >> warp) & 1u;
             uint32_t m = __ballot_sync(0xffffffffu, hit);
             while (m) {
                 const int top = 31 - __clz(m);
@@ -182,11 +179,12 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
 
 void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2* ranges, const uint32_t* point_list,
                             int W, int H, const float4* packed, const float* bg, const float* final_T,
-                            const uint32_t* n_contrib, const float* dL_dpix, float* grad_acc, cudaStream_t st) {
+                            const uint32_t* n_contrib, const float* dL_dpix, float* grad_acc, const uint8_t* warp_mask,
+                            cudaStream_t st) {
     if (row_end <= row_begin || grid_x <= 0) return;
     dim3 grid(grid_x, row_end - row_begin, 1);
     render_bwd_kernel<<<grid, 256, 0, st>>>(ranges, point_list, W, H, grid_x, row_begin, packed, bg, final_T, n_contrib,
-                                             dL_dpix, grad_acc);
+                                             dL_dpix, grad_acc, warp_mask);
     count_launch(1);
 }
 
