@@ -196,9 +196,13 @@ def run_gpu(args):
     if mod is None:
         return run_cpu_reference(args, rank, world)
     P, W, H, deg, M, do_bwd = WORKLOADS[args.workload]
+    if args.P:
+        P = args.P                                                       # C3-style sweep over the model size
     cam0 = S.make_camera(W, H)
     scene = S.make_scene(P, cam0, sh_degree=deg, M=M, seed=0)           # identical on every rank (replicated parameters)
-    cam = ring_camera(S, W, H, rank if world > 1 else None)
+    # fwd+bwd: one camera per rank (multi-view training); render-only: ONE frame, its tile rows split over the ranks
+    cam = ring_camera(S, W, H, rank if (world > 1 and do_bwd) else None)
+    sharded = world > 1 and not do_bwd and args.impl == "b200"
     view = View(mod, cam, scene, device)
     dL_host = torch.from_numpy(S.upstream_grad(cam, seed=1 + rank)).pin_memory()
     dL = dL_host.to(device)
@@ -211,13 +215,24 @@ def run_gpu(args):
     if fused:
         MG.enable_multiview_training(P, device)
 
+    def render_only():
+        with torch.no_grad():
+            if sharded:
+                p = view.params
+                img, radii, band = MG.render_tile_row_sharded(mod.GaussianRasterizer, view.rast.raster_settings, means3D=p["means3D"],
+                                                              means2D=view.means2D, opacities=p["opacities"], shs=p["shs"],
+                                                              scales=p["scales"], rotations=p["rotations"])
+                return img
+            return view.forward()[0]
+
     def step_device():
+        if not do_bwd:
+            return render_only()
         view.zero_grad()
         color, radii = view.forward()
-        if do_bwd:
-            color.backward(dL)
-            if world > 1 and not fused and not args.no_exchange:
-                MG.allreduce_gradients(view.grads())
+        color.backward(dL)
+        if world > 1 and not fused and not args.no_exchange:
+            MG.allreduce_gradients(view.grads())
         return color
 
     def barrier():
@@ -286,9 +301,16 @@ def run_gpu(args):
     # scalar loss back.  The Gaussians are the model's parameters and stay resident, as in the reference (nn.Parameters
     # on cuda, scene/gaussian_model.py:183-204).
     loss_host = torch.zeros(1).pin_memory()
+    img_host = torch.zeros(3, H, W).pin_memory() if not do_bwd else None
 
     def step_e2e():
         view.cam_dev.copy_(view.cam_host, non_blocking=True)
+        if not do_bwd:                       # render-only: the result a viewer needs is the frame itself
+            img = render_only()
+            if rank == 0:                    # the viewer sits on one host: one device-to-host copy of the frame
+                img_host.copy_(img, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return
         dL.copy_(dL_host, non_blocking=True)
         view.zero_grad()
         color, radii = view.forward()
@@ -308,27 +330,34 @@ def run_gpu(args):
     clocks = sampler.stop() if sampler else None
 
     per_step = total_ms / args.steps
+    nviews = world if do_bwd else 1          # render-only: one frame per step however many GPUs share it (strong scaling)
     out = {
-        "metric": "views/s, rasterizer fwd+bwd" if do_bwd else "views/s, rasterizer forward (render only)",
-        "value": world * 1000.0 / per_step, "unit": "views/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": per_step, "higher_is_better": True, "scaling": "weak",
+        "metric": "views/s, rasterizer fwd+bwd" if do_bwd else "frames/s, rasterizer forward (render only)",
+        "value": nviews * 1000.0 / per_step, "unit": "views/s" if do_bwd else "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": per_step, "higher_is_better": True, "scaling": "weak" if do_bwd else "strong",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "impl": args.impl,
-        "config": {"workload": "%s: %d Gaussians, SH degree %d (M=%d), %dx%d, %s, 1 view per GPU per step%s" % (
-            args.workload, P, deg, M, W, H, "fwd+bwd" if do_bwd else "forward only",
-            "" if world == 1 else (", fused SH-gradient exchange over peer memory + NCCL all-reduce of the 14 small floats" if fused
+        "config": {"workload": "%s: %d Gaussians, SH degree %d (M=%d), %dx%d, %s%s" % (
+            args.workload, P, deg, M, W, H, "fwd+bwd, 1 view per GPU per step" if do_bwd else
+            ("forward only, one frame per step" + (", tile rows sharded over the GPUs + all-gather of the bands" if sharded else
+                                                  (", every rank renders the full frame (no sharding in this implementation)" if world > 1 else ""))),
+            "" if (world == 1 or not do_bwd) else (", fused SH-gradient exchange over peer memory + NCCL all-reduce of the 14 small floats" if fused
                                    else ", NCCL all-reduce of per-Gaussian gradients")),
             "P": P, "width": W, "height": H, "sh_degree": deg, "num_rendered": R, "visible": visible,
             "cache": "inputs larger than L2 (%.0f MB of Gaussian parameters per step vs 126 MB L2)" % (P * (3 + 3 + 4 + 1 + 3 * M) * 4 / 1e6)},
         "fwd_ms": fwd_ms, "bwd_ms": bwd_ms,
-        "e2e": {"value": world * 1000.0 / (e2e_ms / args.steps), "unit": "views/s", "ms_per_step": e2e_ms / args.steps,
-                "h2d_bytes_per_step": int(view.cam_host.numel() * 4 + dL_host.numel() * 4), "d2h_bytes_per_step": 4,
-                "what": "GaussianRasterizer.forward + loss + backward through the drop-in Python API; camera and upstream "
-                        "image copied from pinned host memory every step, scalar loss read back; parameters resident"},
+        "e2e": {"value": nviews * 1000.0 / (e2e_ms / args.steps), "unit": "views/s" if do_bwd else "frames/s",
+                "ms_per_step": e2e_ms / args.steps,
+                "h2d_bytes_per_step": int(view.cam_host.numel() * 4 + (dL_host.numel() * 4 if do_bwd else 0)),
+                "d2h_bytes_per_step": 4 if do_bwd else int(3 * H * W * 4),
+                "what": ("GaussianRasterizer.forward + loss + backward through the drop-in Python API; camera and upstream "
+                         "image copied from pinned host memory every step, scalar loss read back; parameters resident") if do_bwd else
+                        "camera copied from pinned host memory, frame rendered through the drop-in Python API and copied back to "
+                        "pinned host memory every step; parameters resident"},
         "gpu_launches": launches,
         "clocks": clocks,
     }
-    if lib:
+    if lib and not sharded:
         out.update(roofline_block(stage, P, R, W * H, visible, (deg + 1) ** 2, hbm_peak, peak_src, args.steps))
     if rank == 0 and world == 1 and args.impl == "b200" and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(R_full=R, P_full=P)
@@ -375,6 +404,12 @@ def roofline_block(stage, P, R, N, P_vis, K, hbm_peak, peak_src, steps):
           "peak_source": peak_src, "launch_ms": stages[dom]["ms"], "alg_bytes_per_launch": stages[dom]["alg_bytes"],
           "note": "the blending kernels are issue-slot/MUFU/shared-memory bound, not HBM bound (SURVEY.md 8(d)); the HBM "
                   "fraction is reported as the contract asks, the pair rate against the FP32-issue bound is in pair_rate"}
+    tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")        # dram bytes per launch from the committed ncu --set full capture
+    if os.path.exists(tpath):
+        t = json.load(open(tpath))
+        if t.get("P") == P and t.get("num_rendered") == R and rl["kernel"] in t.get("kernels", {}):
+            rl["traffic"] = t["kernels"][rl["kernel"]]
+            rl["traffic_source"] = t.get("source")
     out = {"roofline": rl, "stages": stages}
     if dom in ("render", "render_bwd"):
         issue_peak = 148 * 128 * 1.965e9          # lane-instructions/s
@@ -435,6 +470,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--P", type=int, default=0, help="override the number of Gaussians (model-size sweep, BASELINE configs[2])")
     ap.add_argument("--no-exchange", action="store_true", help="diagnostic: N > 1 without any gradient exchange (rank skew only)")
     ap.add_argument("--plain-allreduce", action="store_true", help="N > 1: one NCCL all-reduce of the whole gradient arena "
                     "instead of the fused SH-gradient exchange")

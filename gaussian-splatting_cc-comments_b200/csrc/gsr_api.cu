@@ -216,7 +216,9 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
             shifts[pass] = shift;
             shift += bits[pass];
         }
-        radix_sort_u32(bin.keys, bin.vals, s, R, npass, shifts, bits, bin.table, st);
+        // one histogram launch per pass here: the fused histogram of both tile digits measured slower at R = 12 M
+        // (0.075 ms vs 2 x 0.019 ms; the runs of equal high digits serialise on one shared-memory counter)
+        for (int pass = 0; pass < npass; pass++) radix_sort_u32(bin.keys, bin.vals, s ^ (pass & 1), R, 1, shifts + pass, bits + pass, bin.table, st);
     }
     GSR_STAGE("tile sort", st, a->debug);
     { StageTimer t(ST_RANGES, st); launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st); }

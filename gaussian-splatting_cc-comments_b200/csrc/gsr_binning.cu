@@ -155,12 +155,13 @@ struct RsPasses { int n; int shift[4]; int bits[4]; };
 
 // Digit histograms of ALL passes of one sort in a single read of the keys (the key set does not change between
 // passes, only its order).  ghist[p*256 + d] += count of keys whose pass-p digit is d.
+template <int NP>
 __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __restrict__ keys, size_t n, RsPasses ps,
                                                              uint32_t* __restrict__ ghist) {
-    extern __shared__ uint32_t s_hist[];          // [8 warps][ps.n][RS_BINS]
+    __shared__ uint32_t s_hist[8 * NP * RS_BINS];          // [8 warps][NP][RS_BINS]
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    uint32_t* wh = s_hist + w * ps.n * RS_BINS;
-    for (int i = lane; i < ps.n * RS_BINS; i += 32) wh[i] = 0;
+    uint32_t* wh = s_hist + w * NP * RS_BINS;
+    for (int i = lane; i < NP * RS_BINS; i += 32) wh[i] = 0;
     __syncwarp();
     const size_t n4 = n >> 2;
     const uint4* k4 = reinterpret_cast<const uint4*>(keys);
@@ -170,7 +171,8 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __r
         const bool ok = i < n4;
         const uint4 q = ok ? __ldg(k4 + i) : make_uint4(0, 0, 0, 0);
         const uint32_t kk[4] = {q.x, q.y, q.z, q.w};
-        for (int p = 0; p < ps.n; p++) {
+#pragma unroll
+        for (int p = 0; p < NP; p++) {
             const uint32_t mask = (1u << ps.bits[p]) - 1u;
             uint32_t* hp = wh + p * RS_BINS;
 #pragma unroll
@@ -186,14 +188,16 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __r
     }
     if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
         const uint32_t key = keys[4 * n4 + threadIdx.x];
-        for (int p = 0; p < ps.n; p++) atomicAdd(&wh[p * RS_BINS + ((key >> ps.shift[p]) & ((1u << ps.bits[p]) - 1u))], 1u);
+#pragma unroll
+        for (int p = 0; p < NP; p++) atomicAdd(&wh[p * RS_BINS + ((key >> ps.shift[p]) & ((1u << ps.bits[p]) - 1u))], 1u);
     }
     __syncthreads();
     const int d = threadIdx.x;   // RS_THREADS == RS_BINS
-    for (int p = 0; p < ps.n; p++) {
+#pragma unroll
+    for (int p = 0; p < NP; p++) {
         uint32_t c = 0;
 #pragma unroll
-        for (int ww = 0; ww < 8; ww++) c += s_hist[(ww * ps.n + p) * RS_BINS + d];
+        for (int ww = 0; ww < 8; ww++) c += s_hist[(ww * NP + p) * RS_BINS + d];
         if (c) atomicAdd(&ghist[p * RS_BINS + d], c);
     }
 }
@@ -313,7 +317,12 @@ void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, si
     ps.n = npass;
     for (int p = 0; p < 4; p++) { ps.shift[p] = p < npass ? shifts[p] : 0; ps.bits[p] = p < npass ? bits[p] : 1; }
     const unsigned hb = (unsigned)min((size_t)(148 * 8), (n / 4 + RS_THREADS - 1) / RS_THREADS + 1);
-    rs_hist_kernel<<<hb, RS_THREADS, (size_t)8 * npass * RS_BINS * sizeof(uint32_t), st>>>(keys[s0], n, ps, table);
+    switch (npass) {
+        case 1: rs_hist_kernel<1><<<hb, RS_THREADS, 0, st>>>(keys[s0], n, ps, table); break;
+        case 2: rs_hist_kernel<2><<<hb, RS_THREADS, 0, st>>>(keys[s0], n, ps, table); break;
+        case 3: rs_hist_kernel<3><<<hb, RS_THREADS, 0, st>>>(keys[s0], n, ps, table); break;
+        default: rs_hist_kernel<4><<<hb, RS_THREADS, 0, st>>>(keys[s0], n, ps, table); break;
+    }
     int s = s0;
     for (int p = 0; p < npass; p++) {
         rs_sweep_kernel<<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],

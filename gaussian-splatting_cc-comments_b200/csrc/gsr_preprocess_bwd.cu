@@ -194,14 +194,6 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
     float* g = o.g; float* dmean = o.dmean; float* dcov = o.dcov;
     const float4* ga = reinterpret_cast<const float4*>(a.grad_acc + 12 * (size_t)idx);
     const float4 g0 = ga[0], g1 = ga[1];
-    {   // the blending backward reduced moments (gsr_render_bwd.cu); combine them with this Gaussian's conic:
-        // dL_dmean2D = -(conic * [sum w dx, sum w dy]) * (W/2, H/2), dL_dconic = -1/2 [sum w dx dx, sum w dx dy, sum w dy dy]
-        const float4 pa = __ldg(a.packed + 3 * (size_t)idx);          // x, y, conic.x, conic.y
-        const float conz = __ldg(reinterpret_cast<const float*>(a.packed + 3 * (size_t)idx + 1));
-        g[0] = (-g0.x * pa.z - g0.y * pa.w) * (0.5f * a.W);           // backward.cu:587
-        g[1] = (-g0.y * conz - g0.x * pa.w) * (0.5f * a.H);           // backward.cu:588
-        g[2] = -0.5f * g0.z; g[3] = -0.5f * g0.w; g[4] = -0.5f * g1.x;
-    }
     g[5] = g1.y; g[6] = g1.z; g[7] = g1.w;
     g[8] = a.grad_acc[12 * (size_t)idx + 8];
     const float mx = __ldg(a.means3D + i3), my = __ldg(a.means3D + i3 + 1), mz = __ldg(a.means3D + i3 + 2);
@@ -220,6 +212,16 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
     // ---- computeCov2DCUDA (backward.cu:144-277) ----
     const EwaT e = ewa_T(mx, my, mz, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, V);
     const float3 cov = ewa_cov2d(e, c3);
+    {   // The blending backward reduced moments (gsr_render_bwd.cu); combine them with this Gaussian's conic, rebuilt
+        // with the forward's exact arithmetic (gsr_preprocess.cu) instead of re-read from the 48-byte record:
+        // dL_dmean2D = -(conic * [sum w dx, sum w dy]) * (W/2, H/2), dL_dconic = -1/2 [sum w dx dx, sum w dx dy, sum w dy dy]
+        const float det = fmar(cov.x, cov.z, -mulr(cov.y, cov.y));
+        const float det_inv = __frcp_rn(det);
+        const float conx = mulr(cov.z, det_inv), cony = mulr(cov.y, -det_inv), conz = mulr(cov.x, det_inv);
+        g[0] = (-g0.x * conx - g0.y * cony) * (0.5f * a.W);           // backward.cu:587
+        g[1] = (-g0.y * conz - g0.x * cony) * (0.5f * a.H);           // backward.cu:588
+        g[2] = -0.5f * g0.z; g[3] = -0.5f * g0.w; g[4] = -0.5f * g1.x;
+    }
     const float limx = 1.3f * a.tan_fovx, limy = 1.3f * a.tan_fovy;
     const float txtz = e.tx / e.tz, tytz = e.ty / e.tz;
     const float x_grad_mul = (txtz < -limx || txtz > limx) ? 0.f : 1.f;
