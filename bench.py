@@ -362,8 +362,10 @@ def run_gpu(args):
     if rank == 0 and world == 1 and args.impl == "b200" and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(R_full=R, P_full=P)
     if args.impl == "reference":
-        out["cpu_baseline"] = None
         out["reference_kind"] = "reference CUDA rasterizer, unmodified sources built for sm_100 (oracle/_ref), same GPU"
+        out["cpu_baseline"] = {"value": out["value"], "unit": out["unit"], "cores": 0, "kind": "reference",
+                               "sample": "not a CPU run: the reference ships no CPU rasterizer (SURVEY.md 8(d)); this arm is its unmodified "
+                                         "CUDA rasterizer rebuilt for sm_100 on the same GPU, full workload, same harness"}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
