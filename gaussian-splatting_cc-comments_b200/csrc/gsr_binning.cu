@@ -13,6 +13,7 @@
 // Stability of (2) keeps depth order (and index order among equal depths) inside each tile.
 // All of it is HBM-bound integer work: coalesced key loads, warp-level match_any ranking in
 // shared memory, no tensor cores.
+#include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
 
@@ -202,6 +203,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __r
     }
 }
 
+template <bool BALLOT>
 __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
                                                               uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, size_t n,
                                                               int shift, int bits, const uint32_t* __restrict__ ghist,
@@ -239,7 +241,18 @@ __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __
     for (int r = 0; r < RS_ITEMS; r++) {
         const bool valid = wofs + r * 32 + lane < tile_n;
         const uint32_t d = valid ? ((key[r] >> shift) & mask) : 0xFFFFFFFFu;
-        const uint32_t peers = __match_any_sync(0xffffffffu, d);
+        uint32_t peers;
+        if (BALLOT) {
+            peers = __ballot_sync(0xffffffffu, valid);
+#pragma unroll 8
+            for (int b = 0; b < bits; b++) {
+                const bool one = (d >> b) & 1u;
+                const uint32_t mb = __ballot_sync(0xffffffffu, one);
+                peers &= one ? mb : ~mb;
+            }
+        } else {
+            peers = __match_any_sync(0xffffffffu, d);
+        }
         const int leader = __ffs(peers) - 1;
         uint32_t old = 0;
         if (valid && lane == leader) { old = wh[d]; wh[d] = old + __popc(peers); }
@@ -325,7 +338,12 @@ void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, si
     }
     int s = s0;
     for (int p = 0; p < npass; p++) {
-        rs_sweep_kernel<<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
+        static const bool ballot = getenv("GSR_RS_BALLOT") && atoi(getenv("GSR_RS_BALLOT"));   // EXPERIMENT
+        if (ballot)
+            rs_sweep_kernel<true><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
+                                                   table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
+        else
+            rs_sweep_kernel<false><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
                                                    table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
         s ^= 1;
     }

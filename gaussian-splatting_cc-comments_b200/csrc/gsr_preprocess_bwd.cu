@@ -7,6 +7,7 @@
 // radii <= 0), so callers need no 300 B/Gaussian zero-fill (rasterize_points.cu:168-178).
 // cov3D is recomputed from scale/rotation with the forward's exact arithmetic instead of being
 // stored in the forward and re-read here.  HBM-bound.
+#include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
 #include "gsr_smem.cuh"
@@ -177,11 +178,39 @@ struct BwdOut { float g[9]; float dmean[3]; float dcov[6]; float dscale[3]; floa
 
 // The per-Gaussian backward math.  `sh_row` / `dsh_row` are this Gaussian's SH coefficients and SH-gradient
 // row: global pointers in the generic kernel, the same shared-memory row in the staged kernel.
+// Per-Gaussian inputs, fetched up front so their latency overlaps the cooperative SH-row load.
+struct BwdIn {
+    float4 g0, g1; float g8;
+    float mx, my, mz;
+    float4 q; float sx, sy, sz;
+    uint32_t cl;
+    bool vis;
+};
+
+template <bool VEC>
+__device__ __forceinline__ void load_inputs(const PreprocessBwdArgs& a, int idx, bool vis, BwdIn& in) {
+    in.vis = vis;
+    in.g0 = in.g1 = in.q = make_float4(0, 0, 0, 0);
+    in.g8 = in.mx = in.my = in.mz = in.sx = in.sy = in.sz = 0.f; in.cl = 0;
+    if (!vis) return;
+    const size_t i3 = 3 * (size_t)idx;
+    const float4* ga = reinterpret_cast<const float4*>(a.grad_acc + 12 * (size_t)idx);
+    in.g0 = ga[0]; in.g1 = ga[1];
+    in.g8 = a.grad_acc[12 * (size_t)idx + 8];
+    in.mx = __ldg(a.means3D + i3); in.my = __ldg(a.means3D + i3 + 1); in.mz = __ldg(a.means3D + i3 + 2);
+    if (a.cov3D_precomp == nullptr) {
+        if (VEC) in.q = __ldg(reinterpret_cast<const float4*>(a.rotations) + idx);
+        else in.q = make_float4(__ldg(a.rotations + 4 * (size_t)idx), __ldg(a.rotations + 4 * (size_t)idx + 1),
+                                __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
+        in.sx = __ldg(a.scales + i3); in.sy = __ldg(a.scales + i3 + 1); in.sz = __ldg(a.scales + i3 + 2);
+    }
+    if (a.shs != nullptr) in.cl = a.clamped[idx];
+}
+
 // Returns the number of SH coefficients written to dsh_row (0 when not visible or no SHs).
 template <bool SMEM>
-__device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, const float* V, const float* Pm,
+__device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, const BwdIn& in, const float* V, const float* Pm,
                                        const float* sh_row, float* dsh_row, BwdOut& o) {
-    const size_t i3 = 3 * (size_t)idx;
 #pragma unroll
     for (int i = 0; i < 9; i++) o.g[i] = 0.f;
 #pragma unroll
@@ -190,23 +219,19 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
     for (int i = 0; i < 6; i++) o.dcov[i] = 0.f;
 #pragma unroll
     for (int i = 0; i < 4; i++) o.drot[i] = 0.f;
-    if (!(a.radii[idx] > 0)) return 0;
+    if (!in.vis) return 0;
     float* g = o.g; float* dmean = o.dmean; float* dcov = o.dcov;
-    const float4* ga = reinterpret_cast<const float4*>(a.grad_acc + 12 * (size_t)idx);
-    const float4 g0 = ga[0], g1 = ga[1];
+    const float4 g0 = in.g0, g1 = in.g1;
     g[5] = g1.y; g[6] = g1.z; g[7] = g1.w;
-    g[8] = a.grad_acc[12 * (size_t)idx + 8];
-    const float mx = __ldg(a.means3D + i3), my = __ldg(a.means3D + i3 + 1), mz = __ldg(a.means3D + i3 + 2);
+    g[8] = in.g8;
+    const float mx = in.mx, my = in.my, mz = in.mz;
     float c3[6];
-    float4 q = make_float4(0, 0, 0, 0);
-    float sx = 0, sy = 0, sz = 0;
+    const float4 q = in.q;
+    const float sx = in.sx, sy = in.sy, sz = in.sz;
     if (a.cov3D_precomp != nullptr) {
 #pragma unroll
         for (int i = 0; i < 6; i++) c3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
     } else {
-        q = make_float4(__ldg(a.rotations + 4 * (size_t)idx), __ldg(a.rotations + 4 * (size_t)idx + 1),
-                        __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
-        sx = __ldg(a.scales + i3); sy = __ldg(a.scales + i3 + 1); sz = __ldg(a.scales + i3 + 2);
         cov3d_from_scale_rot(sx, sy, sz, a.scale_modifier, q, c3);
     }
     // ---- computeCov2DCUDA (backward.cu:144-277) ----
@@ -273,7 +298,7 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
     // ---- SH (backward.cu:392-394) ----
     int sh_written = 0;
     if (a.shs != nullptr) {
-        const uint32_t cl = a.clamped[idx];
+        const uint32_t cl = in.cl;
         const F3 dRGB = f3((cl & 1) ? 0.f : g[6], (cl & 2) ? 0.f : g[7], (cl & 4) ? 0.f : g[8]);
         const F3 dir = f3(subr(mx, V[32]), subr(my, V[33]), subr(mz, V[34]));
         o.drgb[0] = dRGB.x; o.drgb[1] = dRGB.y; o.drgb[2] = dRGB.z;
@@ -313,7 +338,9 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
     const size_t i3 = 3 * (size_t)idx;
     float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
     BwdOut o;
-    const int sh_written = bwd_one<false>(a, idx, s_cam, s_cam + 16, a.shs ? a.shs + (size_t)idx * a.M * 3 : nullptr, dsh, o);
+    BwdIn in;
+    load_inputs<false>(a, idx, a.radii[idx] > 0, in);
+    const int sh_written = bwd_one<false>(a, idx, in, s_cam, s_cam + 16, a.shs ? a.shs + (size_t)idx * a.M * 3 : nullptr, dsh, o);
     // ---- write everything (zeros where the reference's pre-zeroed tensors stay untouched) ----
     a.dL_dmean2D[i3] = o.g[0]; a.dL_dmean2D[i3 + 1] = o.g[1]; a.dL_dmean2D[i3 + 2] = 0.f;
     if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(o.g[2], o.g[3], 0.f, o.g[4]);
@@ -344,7 +371,8 @@ __device__ __forceinline__ void copy_out(float* __restrict__ dst, const float* _
     for (int i = 4 * n4 + threadIdx.x; i < n; i += PB) dst[i] = src[i];
 }
 
-__global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwdArgs a, int S /* smem row stride, floats */) {
+template <int MINB>
+__global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(PreprocessBwdArgs a, int S /* smem row stride, floats */) {
     __shared__ float s_cam[36];
     __shared__ uint8_t s_vis[PB];
     extern __shared__ __align__(16) float s_dyn[];     // SH rows (PB x S), later re-used for the 27 other outputs
@@ -356,8 +384,11 @@ __global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwd
     const int t = threadIdx.x;
     const int idx = row0 + t;
     const bool valid = t < nrows;
-    s_vis[t] = valid && (a.radii[idx] > 0);
+    const bool vis = valid && (a.radii[idx] > 0);
+    s_vis[t] = vis;
     __syncthreads();
+    BwdIn in;
+    load_inputs<true>(a, idx, vis, in);
     const int L = 3 * a.M;
     const int Kf = 3 * (a.D + 1) * (a.D + 1);               // live floats per row
     const int Kf4 = (Kf + 3) & ~3;
@@ -367,17 +398,23 @@ __global__ void __launch_bounds__(PB) preprocess_bwd_kernel_staged(PreprocessBwd
         const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)row0 * L);
         const int n4 = nrows * L / 4;
         int f = 4 * t, row = f / L, col = f - row * L;
+        // asynchronous 16-byte copies (LDGSTS): every thread has all of its row pieces in flight at once, next to
+        // the per-Gaussian loads issued above
+        const uint32_t sh_base = smem_addr(s_sh);
         for (int e4 = t; e4 < n4; e4 += PB) {
-            if (s_vis[row] && col < Kf4) *reinterpret_cast<float4*>(s_sh + row * S + col) = __ldg(src + e4);
+            if (s_vis[row] && col < Kf4)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sh_base + 4u * (uint32_t)(row * S + col)), "l"(src + e4) : "memory");
             row += qstep; col += rstep;
             if (col >= L) { col -= L; row++; }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
     }
     BwdOut o;
     if (valid) {
         float* myrow = s_sh + t * S;
-        bwd_one<true>(a, idx, s_cam, s_cam + 16, myrow, myrow, o);
+        bwd_one<true>(a, idx, in, s_cam, s_cam + 16, myrow, myrow, o);
     }
     __syncthreads();
     if (a.dL_dsh != nullptr && L > 0 && !a.skip_dsh) {
@@ -423,9 +460,14 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     const int S = ((L / 4) % 2 == 1 || L == 0) ? L : L + 4;      // 16-byte rows, odd number of 16-byte words: conflict-free
     size_t dyn = (size_t)PB_OUT * sizeof(float);
     if (a.shs && (size_t)PB * S * sizeof(float) > dyn) dyn = (size_t)PB * S * sizeof(float);
-    const bool aligned = (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0;
+    const bool aligned = (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0 &&
+                         (reinterpret_cast<uintptr_t>(a.rotations) & 15) == 0;
     const bool staged = (L % 4 == 0) && aligned && dyn <= 40 * 1024 && (a.M == 0 || a.dL_dsh != nullptr);
-    if (staged) preprocess_bwd_kernel_staged<<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
+    static const int minb = getenv("GSR_PB_MINB") ? atoi(getenv("GSR_PB_MINB")) : 8;   // EXPERIMENT
+    if (staged && minb == 8) preprocess_bwd_kernel_staged<8><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
+    else if (staged && minb == 7) preprocess_bwd_kernel_staged<7><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
+    else if (staged && minb == 5) preprocess_bwd_kernel_staged<5><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
+    else if (staged) preprocess_bwd_kernel_staged<6><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
     else preprocess_bwd_kernel_generic<<<(a.P + 255) / 256, 256, 0, st>>>(a);
     count_launch(1);
 }
