@@ -338,8 +338,8 @@ void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, si
     }
     int s = s0;
     for (int p = 0; p < npass; p++) {
-        static const bool ballot = getenv("GSR_RS_BALLOT") && atoi(getenv("GSR_RS_BALLOT"));   // EXPERIMENT
-        if (ballot)
+        // digits of fewer than 8 bits (the two tile-id passes): per-bit ballots beat match.any; measured on B200
+        if (bits[p] < 8)
             rs_sweep_kernel<true><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
                                                    table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
         else
@@ -385,12 +385,64 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
         }
 }
 
+// Warp-cooperative form: the 32 Gaussians of a warp own one contiguous span of the instance list (offsets are
+// the prefix sum in this same order).  Lanes walk that span 32 entries at a time, find each entry's owner with
+// a 5-step shuffle search over the lanes' span starts, and write keys and ids fully coalesced; a Gaussian that
+// covers hundreds of tiles is spread over the warp instead of serialising one lane.
+__global__ void __launch_bounds__(256) duplicate_coop_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
+                                                             const uint32_t* __restrict__ tt_sorted, const float4* __restrict__ packed,
+                                                             const int* __restrict__ radii, int grid_x, int grid_y, int row_begin, int row_end,
+                                                             uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    uint32_t cnt = 0, g = 0, off = 0, xy0 = 0, w = 1;
+    if (i < P) {
+        cnt = tt_sorted[i];
+        off = offsets[i];
+        if (cnt != 0) {
+            g = order[i];
+            const float4 a = __ldg(packed + 3 * (size_t)g);
+            uint32_t x0, y0, x1, y1;
+            get_rect(a.x, a.y, radii[g], (uint32_t)grid_x, (uint32_t)grid_y, x0, y0, x1, y1);
+            y0 = max(y0, (uint32_t)row_begin);
+            xy0 = x0 | (y0 << 16);
+            w = x1 - x0;
+        }
+    }
+    const uint32_t base = __shfl_sync(0xffffffffu, off, 0);
+    const uint32_t total = __reduce_max_sync(0xffffffffu, (i < P) ? off + cnt - base : 0u);
+    const uint32_t rel = (i < P) ? off - base : 0xFFFFFFFFu;      // non-decreasing over the lanes
+    for (uint32_t k = lane; k < ((total + 31u) & ~31u); k += 32) {
+        int lo = 0;
+        uint32_t rlo = 0;                                          // lane 0 starts at 0
+#pragma unroll
+        for (int step = 16; step > 0; step >>= 1) {
+            const uint32_t r = __shfl_sync(0xffffffffu, rel, lo + step);
+            if (r <= k) { lo += step; rlo = r; }
+        }
+        const uint32_t og = __shfl_sync(0xffffffffu, g, lo);
+        const uint32_t oxy = __shfl_sync(0xffffffffu, xy0, lo);
+        const uint32_t ow = __shfl_sync(0xffffffffu, w, lo);
+        if (k < total) {
+            const uint32_t t = k - rlo;
+            const uint32_t dy = t / ow, dx = t - dy * ow;
+            tile_keys[base + k] = ((oxy >> 16) + dy) * (uint32_t)grid_x + (oxy & 0xFFFFu) + dx;
+            vals[base + k] = og;
+        }
+    }
+}
+
 void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, const uint32_t* tt_sorted,
                       const float4* packed, const int* radii, int grid_x, int grid_y, int row_begin, int row_end,
                       uint32_t* tile_keys, uint32_t* vals, cudaStream_t st) {
     if (P <= 0) return;
-    duplicate_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
-                                                      row_begin, row_end, tile_keys, vals);
+    static const bool coop = !(getenv("GSR_DUP_COOP") && atoi(getenv("GSR_DUP_COOP")) == 0);   // EXPERIMENT
+    if (coop && grid_x < 65536 && grid_y < 65536)
+        duplicate_coop_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
+                                                               row_begin, row_end, tile_keys, vals);
+    else
+        duplicate_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
+                                                          row_begin, row_end, tile_keys, vals);
     count_launch(1);
 }
 

@@ -10,6 +10,7 @@
 //     (3 x st.v4) instead of five separate arrays, plus conservative cull extents,
 //   * cov3D is not stored (the backward recomputes it from scale/rotation),
 //   * the depth-sort key/value pair is emitted here.
+#include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
 #include <stdio.h>
@@ -45,7 +46,8 @@ __device__ __forceinline__ void sh_color_scalar(int K, const float* __restrict__
         for (int ch = 0; ch < 3; ch++) res[ch] = fmar(k[kk], __ldg(sh + 3 * kk + ch), res[ch]);
 }
 
-__global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) preprocess_fwd_kernel(PreprocessArgs a) {
     __shared__ float s_cam[36];
     if (threadIdx.x < 16) s_cam[threadIdx.x] = a.cam.view[threadIdx.x];
     else if (threadIdx.x < 32) s_cam[threadIdx.x] = a.cam.proj[threadIdx.x - 16];
@@ -62,6 +64,16 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
     uint32_t out_key = 0xFFFFFFFFu;   // sorts behind every visible Gaussian; emits nothing
 
     const float mx = __ldg(a.means3D + 3 * idx), my = __ldg(a.means3D + 3 * idx + 1), mz = __ldg(a.means3D + 3 * idx + 2);
+    // every per-Gaussian input except the SH row is fetched up front (one memory round trip instead of three)
+    float4 q_in = make_float4(0.f, 0.f, 0.f, 1.f);
+    float sx_in = 0.f, sy_in = 0.f, sz_in = 0.f;
+    if (a.cov3D_precomp == nullptr) {
+        if ((reinterpret_cast<uintptr_t>(a.rotations) & 15) == 0) q_in = ldg4(a.rotations + 4 * (size_t)idx);
+        else q_in = make_float4(__ldg(a.rotations + 4 * (size_t)idx), __ldg(a.rotations + 4 * (size_t)idx + 1),
+                                __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
+        sx_in = __ldg(a.scales + 3 * idx); sy_in = __ldg(a.scales + 3 * idx + 1); sz_in = __ldg(a.scales + 3 * idx + 2);
+    }
+    const float opacity = __ldg(a.opacities + idx);
     // in_frustum (auxiliary.h:144-175): only the near-plane test is live
     const float depth = dot4(V[2], V[6], V[10], V[14], mx, my, mz);
     bool alive = !(depth <= 0.2f);
@@ -81,12 +93,7 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
 #pragma unroll
             for (int i = 0; i < 6; i++) c3[i] = __ldg(a.cov3D_precomp + 6 * (size_t)idx + i);
         } else {
-            float4 q;
-            if ((reinterpret_cast<uintptr_t>(a.rotations) & 15) == 0) q = ldg4(a.rotations + 4 * (size_t)idx);
-            else q = make_float4(__ldg(a.rotations + 4 * (size_t)idx), __ldg(a.rotations + 4 * (size_t)idx + 1),
-                                 __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
-            cov3d_from_scale_rot(__ldg(a.scales + 3 * idx), __ldg(a.scales + 3 * idx + 1), __ldg(a.scales + 3 * idx + 2),
-                                 a.scale_modifier, q, c3);
+            cov3d_from_scale_rot(sx_in, sy_in, sz_in, a.scale_modifier, q_in, c3);
         }
         const EwaT e = ewa_T(mx, my, mz, a.focal_x, a.focal_y, a.tan_fovx, a.tan_fovy, V);
         const float3 cov = ewa_cov2d(e, c3);
@@ -130,7 +137,6 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
 #pragma unroll
                     for (int ch = 0; ch < 3; ch++) rgb[ch] = __ldg(a.colors_precomp + 3 * (size_t)idx + ch);
                 }
-                const float opacity = __ldg(a.opacities + idx);
 
                 // ---- conservative cull data for the blending kernels ------------------------------
                 // alpha = min(.99, o*exp(power)) >= 1/255 needs power >= -ln(255 o).  The ellipse
@@ -171,7 +177,10 @@ __global__ void __launch_bounds__(256) preprocess_fwd_kernel(PreprocessArgs a) {
 
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
-    preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    static const int minb = getenv("GSR_PF_MINB") ? atoi(getenv("GSR_PF_MINB")) : 4;   // EXPERIMENT
+    if (minb == 4) preprocess_fwd_kernel<4><<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    else if (minb == 5) preprocess_fwd_kernel<5><<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    else preprocess_fwd_kernel<2><<<(a.P + 255) / 256, 256, 0, st>>>(a);
     count_launch(1);
 }
 
