@@ -281,7 +281,7 @@ def run_gpu(args):
     fwd_ms = bwd_ms = None
     if do_bwd:
         ef = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-        acc_f = acc_b = 0.0
+        fs, bs = [], []
         n_split = min(args.steps, 10)
         for _ in range(n_split):
             view.zero_grad()
@@ -292,8 +292,10 @@ def run_gpu(args):
             color.backward(dL)
             ef[2].record()
             torch.cuda.synchronize()
-            acc_f += ef[0].elapsed_time(ef[1]); acc_b += ef[1].elapsed_time(ef[2])
-        fwd_ms, bwd_ms = acc_f / n_split, acc_b / n_split
+            fs.append(ef[0].elapsed_time(ef[1])); bs.append(ef[1].elapsed_time(ef[2]))
+        fwd_ms, bwd_ms = float(np.median(fs)), float(np.median(bs))
+        if rank == 0:
+            print("split fwd ms:", ["%.3f" % x for x in fs], "bwd ms:", ["%.3f" % x for x in bs], file=sys.stderr)
 
     # ---- timed region 2: end to end through the public API with host buffers ("e2e") --------------------------------
     # Per step the host supplies what changes per view in train.py -- the camera (35 floats) and the per-pixel
@@ -302,6 +304,8 @@ def run_gpu(args):
     # on cuda, scene/gaussian_model.py:183-204).
     loss_host = torch.zeros(1).pin_memory()
     img_host = torch.zeros(3, H, W).pin_memory() if not do_bwd else None
+    copy_stream = torch.cuda.Stream(device=device)
+    copied = torch.cuda.Event()
 
     def step_e2e():
         view.cam_dev.copy_(view.cam_host, non_blocking=True)
@@ -311,9 +315,14 @@ def run_gpu(args):
                 img_host.copy_(img, non_blocking=True)
             torch.cuda.current_stream().synchronize()
             return
-        dL.copy_(dL_host, non_blocking=True)
+        # the upstream image (the stand-in for the next ground-truth image) rides a copy stream while the forward runs,
+        # as a training loop prefetches its next target; the previous step's readers of dL finished at its final sync
+        with torch.cuda.stream(copy_stream):
+            dL.copy_(dL_host, non_blocking=True)
+            copied.record(copy_stream)
         view.zero_grad()
         color, radii = view.forward()
+        torch.cuda.current_stream().wait_event(copied)
         if do_bwd:
             loss = (color * dL).sum()
             loss.backward()

@@ -6,6 +6,7 @@
 // -- reading num_rendered to size the binning buffer, rasterizer_impl.cu:331 -- is kept because
 // the API returns it as an int; it is a 4-byte async copy into pinned memory + stream sync.
 #include "../../include/gsr.h"
+#include <cstdlib>
 #include "gsr_internal.cuh"
 #include <string>
 #include <cstdio>
@@ -57,6 +58,10 @@ struct StageTimer {        // records start/stop events around one stage on the 
 
 static thread_local std::string g_err;
 static thread_local uint32_t* g_pinned = nullptr;
+
+// Side stream + events for reading num_rendered back while the depth sort runs (one set per device and host thread).
+struct Readback { cudaStream_t side = nullptr; cudaEvent_t produced = nullptr, copied = nullptr; };
+static thread_local Readback g_readback[GSR_MAX_DEVICES];
 
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 
@@ -170,26 +175,44 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     pa.prefiltered = a->prefiltered;
     pa.radii = radii; pa.packed = geom.packed; pa.tiles_touched = geom.tiles_touched; pa.clamped = geom.clamped;
     pa.depth_keys = geom.keys[0]; pa.ids = geom.vals[0];
+    pa.total = geom.total;
+    GSR_CUDA(cudaMemsetAsync(geom.total, 0, sizeof(uint32_t), st));
     { StageTimer t(ST_PREPROCESS, st); launch_preprocess(pa, st); }
     GSR_STAGE("preprocess", st, a->debug);
+
+    // num_rendered is final once preprocess is done (a sum does not care about the depth order): copy it to the host
+    // on a side stream now, so the round trip and the binning-buffer resize hide behind the depth sort
+    int dev = 0;
+    GSR_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= GSR_MAX_DEVICES) return fail(GSR_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+    Readback& rbk = g_readback[dev];
+    if (!rbk.side) {
+        GSR_CUDA(cudaStreamCreateWithFlags(&rbk.side, cudaStreamNonBlocking));
+        GSR_CUDA(cudaEventCreateWithFlags(&rbk.produced, cudaEventDisableTiming));
+        GSR_CUDA(cudaEventCreateWithFlags(&rbk.copied, cudaEventDisableTiming));
+    }
+    if (!g_pinned) GSR_CUDA(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
+    GSR_CUDA(cudaEventRecord(rbk.produced, st));
+    GSR_CUDA(cudaStreamWaitEvent(rbk.side, rbk.produced, 0));
+    GSR_CUDA(cudaMemcpyAsync(g_pinned, geom.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, rbk.side));
+    GSR_CUDA(cudaEventRecord(rbk.copied, rbk.side));
 
     // depth order of the Gaussians: 4 stable 8-bit passes, result back in keys[0]/vals[0]
     {
         StageTimer t(ST_DEPTH_SORT, st);
         const int shifts[4] = {0, 8, 16, 24}, bits[4] = {8, 8, 8, 8};
-        radix_sort_u32(geom.keys, geom.vals, 0, P, 4, shifts, bits, geom.table, st);
+        static const int items_d = getenv("GSR_RS_ITEMS_D") ? atoi(getenv("GSR_RS_ITEMS_D")) : 16;   // EXPERIMENT
+        radix_sort_u32(geom.keys, geom.vals, 0, P, 4, shifts, bits, geom.table, items_d, st);
     }
     GSR_STAGE("depth sort", st, a->debug);
     {
         StageTimer t(ST_SCAN, st);
         launch_gather_u32(geom.tiles_touched, geom.vals[0], geom.tt_sorted, P, st);
-        scan_exclusive_u32(geom.tt_sorted, geom.offsets, P, geom.scan_tmp, geom.total, st);
+        scan_exclusive_u32(geom.tt_sorted, geom.offsets, P, geom.scan_tmp, nullptr, st);
     }
     GSR_STAGE("scan", st, a->debug);
 
-    if (!g_pinned) GSR_CUDA(cudaHostAlloc((void**)&g_pinned, 64, cudaHostAllocDefault));
-    GSR_CUDA(cudaMemcpyAsync(g_pinned, geom.total, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
-    GSR_CUDA(cudaStreamSynchronize(st));
+    GSR_CUDA(cudaEventSynchronize(rbk.copied));
     const size_t R = *g_pinned;
     if (R > 0x7fffffffull) return fail(GSR_ERR_INVALID_ARGUMENT, "num_rendered exceeds int range");
 
@@ -218,7 +241,8 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
         }
         // one histogram launch per pass here: the fused histogram of both tile digits measured slower at R = 12 M
         // (0.075 ms vs 2 x 0.019 ms; the runs of equal high digits serialise on one shared-memory counter)
-        for (int pass = 0; pass < npass; pass++) radix_sort_u32(bin.keys, bin.vals, s ^ (pass & 1), R, 1, shifts + pass, bits + pass, bin.table, st);
+        static const int items_t = getenv("GSR_RS_ITEMS_T") ? atoi(getenv("GSR_RS_ITEMS_T")) : 16;   // EXPERIMENT
+        for (int pass = 0; pass < npass; pass++) radix_sort_u32(bin.keys, bin.vals, s ^ (pass & 1), R, 1, shifts + pass, bits + pass, bin.table, items_t, st);
     }
     GSR_STAGE("tile sort", st, a->debug);
     { StageTimer t(ST_RANGES, st); launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st); }

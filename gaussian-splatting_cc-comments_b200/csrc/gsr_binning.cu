@@ -203,14 +203,17 @@ __global__ void __launch_bounds__(RS_THREADS) rs_hist_kernel(const uint32_t* __r
     }
 }
 
-template <bool BALLOT>
-__global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
+#ifndef RS_MINB
+#define RS_MINB 5
+#endif
+template <bool BALLOT, int ITEMS>
+__global__ void __launch_bounds__(RS_THREADS, RS_MINB) rs_sweep_kernel(const uint32_t* __restrict__ kin, const uint32_t* __restrict__ vin,
                                                               uint32_t* __restrict__ kout, uint32_t* __restrict__ vout, size_t n,
                                                               int shift, int bits, const uint32_t* __restrict__ ghist,
                                                               uint32_t* ticket, uint32_t* lookback) {
     __shared__ uint32_t s_hist[8 * RS_BINS];
-    __shared__ uint32_t s_keys[RS_TILE];
-    __shared__ uint32_t s_vals[RS_TILE];
+    __shared__ uint32_t s_keys[(RS_THREADS * ITEMS)];
+    __shared__ uint32_t s_vals[(RS_THREADS * ITEMS)];
     __shared__ uint32_t s_dstart[RS_BINS];     // first local (digit-sorted) position of each digit
     __shared__ uint32_t s_gbase[RS_BINS];      // global position of local position 0 of each digit's run
     __shared__ uint32_t s_warp[RS_THREADS / 32 + 1];
@@ -221,24 +224,24 @@ __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __
     const uint32_t mask = (1u << bits) - 1u;
     const int radix = 1 << bits;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-    const size_t tile_base = (size_t)bid * RS_TILE;
-    const int tile_n = (int)min((size_t)RS_TILE, n - tile_base);
+    const size_t tile_base = (size_t)bid * (RS_THREADS * ITEMS);
+    const int tile_n = (int)min((size_t)(RS_THREADS * ITEMS), n - tile_base);
 
     // ---- rank ----
     uint32_t* wh = s_hist + w * RS_BINS;
     for (int i = lane; i < RS_BINS; i += 32) wh[i] = 0;
-    const int wofs = w * (32 * RS_ITEMS);
-    uint32_t key[RS_ITEMS];
-    uint16_t rank[RS_ITEMS];
+    const int wofs = w * (32 * ITEMS);
+    uint32_t key[ITEMS];
+    uint16_t rank[ITEMS];
 #pragma unroll
-    for (int r = 0; r < RS_ITEMS; r++) {
+    for (int r = 0; r < ITEMS; r++) {
         const int li = wofs + r * 32 + lane;
         key[r] = (li < tile_n) ? kin[tile_base + li] : 0xFFFFFFFFu;
     }
     __syncwarp();
     const uint32_t lt = (1u << lane) - 1u;
 #pragma unroll
-    for (int r = 0; r < RS_ITEMS; r++) {
+    for (int r = 0; r < ITEMS; r++) {
         const bool valid = wofs + r * 32 + lane < tile_n;
         const uint32_t d = valid ? ((key[r] >> shift) & mask) : 0xFFFFFFFFu;
         uint32_t peers;
@@ -295,7 +298,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __
 
     // ---- reorder by digit in shared memory ----
 #pragma unroll
-    for (int r = 0; r < RS_ITEMS; r++) {
+    for (int r = 0; r < ITEMS; r++) {
         const int li = wofs + r * 32 + lane;
         if (li < tile_n) {
             const uint32_t dg = (key[r] >> shift) & mask;
@@ -307,7 +310,7 @@ __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __
     __syncthreads();
     // ---- contiguous runs out ----
 #pragma unroll
-    for (int k = 0; k < RS_ITEMS; k++) {
+    for (int k = 0; k < ITEMS; k++) {
         const int j = k * RS_THREADS + threadIdx.x;
         if (j < tile_n) {
             const uint32_t kk = s_keys[j];
@@ -321,10 +324,19 @@ __global__ void __launch_bounds__(RS_THREADS) rs_sweep_kernel(const uint32_t* __
 // Stable LSD sort of n (key, value) pairs on the given digit passes; input in keys[s0]/vals[s0], the result ends
 // in keys[s0 ^ (npass & 1)].  `table` (rs_table_words(n) words) holds the digit histograms of all passes
 // [p*256, p*256+256), the ticket counters [1024 + p] and one look-back table per pass from word 1280.
+template <bool BALLOT>
+static void launch_sweep(int items, unsigned nb, cudaStream_t st, const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout,
+                         size_t n, int shift, int bits, const uint32_t* ghist, uint32_t* ticket, uint32_t* lookback) {
+    if (items == 8) rs_sweep_kernel<BALLOT, 8><<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, ghist, ticket, lookback);
+    else if (items == 12) rs_sweep_kernel<BALLOT, 12><<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, ghist, ticket, lookback);
+    else rs_sweep_kernel<BALLOT, 16><<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, ghist, ticket, lookback);
+}
+
 void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, size_t n, int npass, const int* shifts,
-                    const int* bits, uint32_t* table, cudaStream_t st) {
+                    const int* bits, uint32_t* table, int items, cudaStream_t st) {
     if (n == 0 || npass <= 0) return;
-    const unsigned nb = (unsigned)rs_blocks(n);
+    if (items != 8 && items != 12) items = 16;
+    const unsigned nb = (unsigned)((n + (size_t)RS_THREADS * items - 1) / ((size_t)RS_THREADS * items));
     cudaMemsetAsync(table, 0, (1280 + (size_t)npass * nb * RS_BINS) * sizeof(uint32_t), st);
     RsPasses ps;
     ps.n = npass;
@@ -340,11 +352,11 @@ void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, si
     for (int p = 0; p < npass; p++) {
         // digits of fewer than 8 bits (the two tile-id passes): per-bit ballots beat match.any; measured on B200
         if (bits[p] < 8)
-            rs_sweep_kernel<true><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
-                                                   table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
+            launch_sweep<true>(items, nb, st, keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
+                               table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
         else
-            rs_sweep_kernel<false><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
-                                                   table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
+            launch_sweep<false>(items, nb, st, keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
+                                table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
         s ^= 1;
     }
     count_launch(1 + npass);
@@ -462,10 +474,40 @@ __global__ void __launch_bounds__(256) tile_ranges_kernel(size_t R, const uint32
     if (i == R - 1) ranges[cur].y = (uint32_t)R;
 }
 
+// four keys per thread (one 16-byte load + the key before them)
+__global__ void __launch_bounds__(256) tile_ranges4_kernel(size_t R, const uint32_t* __restrict__ keys, uint2* __restrict__ ranges) {
+    const size_t i0 = 4 * ((size_t)blockIdx.x * blockDim.x + threadIdx.x);
+    if (i0 >= R) return;
+    uint32_t k[5];
+    k[0] = i0 ? keys[i0 - 1] : 0u;
+    if (i0 + 4 <= R) {
+        const uint4 q = *reinterpret_cast<const uint4*>(keys + i0);
+        k[1] = q.x; k[2] = q.y; k[3] = q.z; k[4] = q.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; j++) k[1 + j] = (i0 + j < R) ? keys[i0 + j] : 0u;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        const size_t i = i0 + j;
+        if (i >= R) break;
+        const uint32_t cur = k[1 + j];
+        if (i == 0) ranges[cur].x = 0;
+        else if (cur != k[j]) {
+            ranges[k[j]].y = (uint32_t)i;
+            ranges[cur].x = (uint32_t)i;
+        }
+        if (i == R - 1) ranges[cur].y = (uint32_t)R;
+    }
+}
+
 void launch_tile_ranges(size_t R, const uint32_t* sorted_tile_keys, uint2* ranges, size_t tiles, cudaStream_t st) {
     cudaMemsetAsync(ranges, 0, tiles * sizeof(uint2), st);
     if (R == 0) return;
-    tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, sorted_tile_keys, ranges);
+    if ((reinterpret_cast<uintptr_t>(sorted_tile_keys) & 15) == 0)
+        tile_ranges4_kernel<<<(unsigned)((R + 1023) / 1024), 256, 0, st>>>(R, sorted_tile_keys, ranges);
+    else
+        tile_ranges_kernel<<<(unsigned)((R + 255) / 256), 256, 0, st>>>(R, sorted_tile_keys, ranges);
     count_launch(1);
 }
 

@@ -56,8 +56,10 @@ __global__ void __launch_bounds__(256, MINB) preprocess_fwd_kernel(PreprocessArg
     const float* V = s_cam;
     const float* Pm = s_cam + 16;
 
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= a.P) return;
+    // threads past the end redo the last Gaussian without storing anything: the whole block reaches the reduction below
+    const int idx_raw = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in_range = idx_raw < a.P;
+    const int idx = in_range ? idx_raw : a.P - 1;
 
     int out_radius = 0;
     uint32_t out_tiles = 0;
@@ -76,8 +78,8 @@ __global__ void __launch_bounds__(256, MINB) preprocess_fwd_kernel(PreprocessArg
     const float opacity = __ldg(a.opacities + idx);
     // in_frustum (auxiliary.h:144-175): only the near-plane test is live
     const float depth = dot4(V[2], V[6], V[10], V[14], mx, my, mz);
-    bool alive = !(depth <= 0.2f);
-    if (!alive && a.prefiltered) {
+    bool alive = in_range && !(depth <= 0.2f);
+    if (in_range && !alive && a.prefiltered) {
         printf("Point is filtered although prefiltered is set. This shouldn't happen!");
         __trap();
     }
@@ -169,10 +171,26 @@ __global__ void __launch_bounds__(256, MINB) preprocess_fwd_kernel(PreprocessArg
             }
         }
     }
-    if (a.radii) a.radii[idx] = out_radius;
-    a.tiles_touched[idx] = out_tiles;
-    a.depth_keys[idx] = out_key;
-    a.ids[idx] = (uint32_t)idx;
+    if (in_range) {
+        if (a.radii) a.radii[idx] = out_radius;
+        a.tiles_touched[idx] = out_tiles;
+        a.depth_keys[idx] = out_key;
+        a.ids[idx] = (uint32_t)idx;
+    }
+    // num_rendered = sum of tiles_touched is known here, long before the sorted prefix sum: the host reads it back
+    // while the depth sort runs (gsr_api.cu)
+    if (a.total != nullptr) {
+        __shared__ uint32_t s_sum[8];
+        const uint32_t wsum = __reduce_add_sync(0xffffffffu, out_tiles);
+        if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = wsum;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t bsum = 0;
+#pragma unroll
+            for (int w = 0; w < 8; w++) bsum += s_sum[w];
+            if (bsum) atomicAdd(a.total, bsum);
+        }
+    }
 }
 
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
