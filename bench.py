@@ -212,8 +212,9 @@ def run_gpu(args):
     # N > 1, this implementation: the fused exchange lives inside backward() (peer-mapped dL/dRGB blocks + one kernel
     # for the SH block, one NCCL all-reduce for the 14 small floats).  The reference arm all-reduces its tensors with NCCL.
     fused = world > 1 and args.impl == "b200" and do_bwd and not args.plain_allreduce and not args.no_exchange
+    mv_exchange = None
     if fused:
-        MG.enable_multiview_training(P, device)
+        mv_exchange = MG.enable_multiview_training(P, device)
 
     def render_only():
         with torch.no_grad():
@@ -272,6 +273,8 @@ def run_gpu(args):
         lib.profiling(True)
         l0 = lib.launches()
     total_ms = timed(step_device, args.steps)
+    if mv_exchange is not None and os.environ.get("GSR_MV_TIMELINE") == "1" and rank == 0:
+        print("exchange timeline (ms from backward start):", json.dumps(mv_exchange.timeline_report()), file=sys.stderr)
     stage = lib.stage_ms() if lib else {}
     launches = (lib.launches() - l0) if lib else None
     if lib:

@@ -307,9 +307,43 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     pb.dL_dmean2D = a->dL_dmean2D; pb.dL_dconic = a->dL_dconic; pb.dL_dopacity = a->dL_dopacity; pb.dL_dcolor = a->dL_dcolor;
     pb.dL_dmean3D = a->dL_dmean3D; pb.dL_dcov3D = a->dL_dcov3D; pb.dL_dsh = a->dL_dsh; pb.dL_dscale = a->dL_dscale; pb.dL_drot = a->dL_drot;
     pb.dL_drgb = early_drgb ? nullptr : a->dL_drgb; pb.skip_dsh = (a->dL_drgb != nullptr && a->skip_dL_dsh) ? 1 : 0;
+    pb.begin = 0; pb.chunked = a->dL_drgb != nullptr;
+    pb.small_pack = a->small_pack;
+    pb.chunk_events = a->chunk_done_events;
+    pb.n_chunk_events = a->chunk_done_events ? (a->n_chunk_events < GSR_MAX_CHUNKS ? a->n_chunk_events : GSR_MAX_CHUNKS) : 0;
     { StageTimer t(ST_PREPROCESS_BWD, st); launch_preprocess_backward(pb, st); }
     GSR_STAGE("preprocess backward", st, a->debug);
     return GSR_OK;
+}
+
+int gsr_unpack_small_grads(int begin, int end, const float* small_pack, float* dL_dmean3D, float* dL_dmean2D,
+                           float* dL_dopacity, float* dL_dscale, float* dL_drot, void* cuda_stream) {
+    if (begin < 0 || end < begin) return fail(GSR_ERR_INVALID_ARGUMENT, "bad range");
+    if (end == begin) return GSR_OK;
+    if (!small_pack || !dL_dmean3D || !dL_dmean2D || !dL_dopacity || !dL_dscale || !dL_drot)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_unpack_small(begin, end, small_pack, dL_dmean3D, dL_dmean2D, dL_dopacity, dL_dscale, dL_drot, st);
+    GSR_STAGE("unpack small gradients", st, 0);
+    return GSR_OK;
+}
+
+int gsr_multimem_allreduce(void* multicast_base, size_t begin, size_t end, int rank, int world, void* cuda_stream) {
+    if (!multicast_base || ((size_t)multicast_base & 15) || (begin & 3) || end < begin || world < 1 || rank < 0 || rank >= world)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "bad multimem all-reduce arguments");
+    static const int max_blocks = getenv("GSR_MM_BLOCKS") ? atoi(getenv("GSR_MM_BLOCKS")) : 148;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_multimem_allreduce((float*)multicast_base, begin, end, rank, world, max_blocks > 0 ? max_blocks : 148, st);
+    GSR_STAGE("multimem all-reduce", st, 0);
+    return GSR_OK;
+}
+
+int gsr_backward_chunk_plan(int P, int* bounds) {
+    if (!bounds || P < 0) return 0;
+    int b[5];
+    const int n = chunk_plan(P, 256, b);
+    for (int i = 0; i <= n; i++) bounds[i] = b[i];
+    return n;
 }
 
 int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* peer_blocks, const float* means3D,
@@ -319,7 +353,7 @@ int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* 
     if (P == 0) return GSR_OK;
     if (!peer_blocks || !means3D || !dL_dsh) return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
     MultiviewShArgs a;
-    a.P = P; a.D = D; a.M = M; a.n_views = n_views; a.means3D = means3D; a.dL_dsh = dL_dsh;
+    a.P = P; a.D = D; a.M = M; a.n_views = n_views; a.means3D = means3D; a.dL_dsh = dL_dsh; a.begin = 0;
     for (int v = 0; v < 16; v++) a.blocks[v] = nullptr;
     for (int v = 0; v < n_views; v++) {
         if (!peer_blocks[v] || ((size_t)peer_blocks[v] & 15)) return fail(GSR_ERR_INVALID_ARGUMENT, "peer block missing or not 16-byte aligned");

@@ -177,7 +177,14 @@ struct PreprocessBwdArgs {
     float* dL_dmean3D; float* dL_dcov3D; float* dL_dsh; float* dL_dscale; float* dL_drot;
     float* dL_drgb;            // optional (P,3): clamp-masked colour gradient (multi-view exchange)
     int skip_dsh;              // leave dL_dsh untouched
+    int begin;                 // first Gaussian of this launch (chunked launches); P is the end bound
+    int chunked;               // a collective runs beside this kernel: launch it in chunks (chunk_plan)
+    void* const* chunk_events; int n_chunk_events;   // optional cudaEvent_t per chunk (see include/gsr.h)
+    float* small_pack;         // optional (P,14): mean3D 3 | mean2D 3 | opacity 1 | scale 3 | rot 4 instead of the five tensors
 };
+void launch_multimem_allreduce(float* mc_base, size_t begin, size_t end, int rank, int world, int max_blocks, cudaStream_t st);
+void launch_unpack_small(int begin, int end, const float* pack, float* dmean3D, float* dmean2D, float* dop, float* dscale,
+                         float* drot, cudaStream_t st);
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st);
 // masked colour gradient (P,3) from the blending accumulators: out = radii > 0 ? acc[6..8] with SH-clamped channels zeroed : 0
 void launch_publish_drgb(int P, const float* grad_acc, const int* radii, const uint8_t* clamped /* NULL: no mask */, float* out,
@@ -188,7 +195,24 @@ struct MultiviewShArgs {
     const float* blocks[16];   // per view: campos (4 floats) then (P,3) masked colour gradients, peer-mapped
     const float* means3D;
     float* dL_dsh;
+    int begin;                 // first Gaussian of this launch (chunked launches); P is the end bound
 };
 void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st);
+
+// Chunked launches for kernels that run beside a collective: a grid of tens of thousands of short blocks keeps every
+// SM full, and the collective's few large CTAs (launched a moment later on another stream) are not placed until that
+// grid drains, whatever the stream priorities.  A small head chunk followed by three equal ones gives the block
+// scheduler drain points where the waiting CTAs get in.  Returns the number of chunks; bounds[i]..bounds[i+1].
+static inline int chunk_plan(int P, int unit, int bounds[5]) {
+    bounds[0] = 0;
+    if (P < 64 * 1024) { bounds[1] = P; return 1; }
+    const int head = ((P / 16 + unit - 1) / unit) * unit;
+    const int part = (((P - head) / 3 + unit - 1) / unit) * unit;
+    bounds[1] = head;
+    bounds[2] = head + part < P ? head + part : P;
+    bounds[3] = head + 2 * part < P ? head + 2 * part : P;
+    bounds[4] = P;
+    return 4;
+}
 
 }  // namespace gsr

@@ -333,7 +333,7 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
     __shared__ float s_cam[36];
     load_camera(a, s_cam);
     __syncthreads();
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = a.begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
     const size_t i3 = 3 * (size_t)idx;
     float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
@@ -342,16 +342,26 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
     load_inputs<false>(a, idx, a.radii[idx] > 0, in);
     const int sh_written = bwd_one<false>(a, idx, in, s_cam, s_cam + 16, a.shs ? a.shs + (size_t)idx * a.M * 3 : nullptr, dsh, o);
     // ---- write everything (zeros where the reference's pre-zeroed tensors stay untouched) ----
-    a.dL_dmean2D[i3] = o.g[0]; a.dL_dmean2D[i3 + 1] = o.g[1]; a.dL_dmean2D[i3 + 2] = 0.f;
     if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(o.g[2], o.g[3], 0.f, o.g[4]);
-    a.dL_dopacity[idx] = o.g[5];
     a.dL_dcolor[i3] = o.g[6]; a.dL_dcolor[i3 + 1] = o.g[7]; a.dL_dcolor[i3 + 2] = o.g[8];
-    a.dL_dmean3D[i3] = o.dmean[0]; a.dL_dmean3D[i3 + 1] = o.dmean[1]; a.dL_dmean3D[i3 + 2] = o.dmean[2];
 #pragma unroll
     for (int i = 0; i < 6; i++) a.dL_dcov3D[6 * (size_t)idx + i] = o.dcov[i];
-    a.dL_dscale[i3] = o.dscale[0]; a.dL_dscale[i3 + 1] = o.dscale[1]; a.dL_dscale[i3 + 2] = o.dscale[2];
+    if (a.small_pack) {
+        float* row = a.small_pack + 14 * (size_t)idx;
+        row[0] = o.dmean[0]; row[1] = o.dmean[1]; row[2] = o.dmean[2];
+        row[3] = o.g[0]; row[4] = o.g[1]; row[5] = 0.f;
+        row[6] = o.g[5];
+        row[7] = o.dscale[0]; row[8] = o.dscale[1]; row[9] = o.dscale[2];
 #pragma unroll
-    for (int i = 0; i < 4; i++) a.dL_drot[4 * (size_t)idx + i] = o.drot[i];
+        for (int i = 0; i < 4; i++) row[10 + i] = o.drot[i];
+    } else {
+        a.dL_dmean2D[i3] = o.g[0]; a.dL_dmean2D[i3 + 1] = o.g[1]; a.dL_dmean2D[i3 + 2] = 0.f;
+        a.dL_dopacity[idx] = o.g[5];
+        a.dL_dmean3D[i3] = o.dmean[0]; a.dL_dmean3D[i3 + 1] = o.dmean[1]; a.dL_dmean3D[i3 + 2] = o.dmean[2];
+        a.dL_dscale[i3] = o.dscale[0]; a.dL_dscale[i3 + 1] = o.dscale[1]; a.dL_dscale[i3 + 2] = o.dscale[2];
+#pragma unroll
+        for (int i = 0; i < 4; i++) a.dL_drot[4 * (size_t)idx + i] = o.drot[i];
+    }
     if (dsh) for (int i = 3 * sh_written; i < 3 * a.M; i++) dsh[i] = 0.f;
     if (a.dL_drgb) { a.dL_drgb[i3] = o.drgb[0]; a.dL_drgb[i3 + 1] = o.drgb[1]; a.dL_drgb[i3 + 2] = o.drgb[2]; }
 }
@@ -363,7 +373,8 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
 // culled Gaussians and for coefficients beyond the active degree).  The 27 other floats per Gaussian are
 // staged the same way, so every global store instruction of a warp covers one contiguous 512-byte span.
 constexpr int PB = 128;
-constexpr int PB_OUT = 30 * PB;     // mean2D 3 | conic 4 | opacity 1 | colour 3 | mean3D 3 | cov3D 6 | scale 3 | rot 4 | masked rgb 3
+// floats of output staging per block; the last 14 per Gaussian are the packed small-gradient rows (multi-view exchange)
+constexpr int PB_OUT = 44 * PB;     // mean2D 3 | conic 4 | opacity 1 | colour 3 | mean3D 3 | cov3D 6 | scale 3 | rot 4 | masked rgb 3
 
 __device__ __forceinline__ void copy_out(float* __restrict__ dst, const float* __restrict__ src, int n) {
     int n4 = ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) ? (n >> 2) : 0;
@@ -379,7 +390,7 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
     float* s_sh = s_dyn;
     float* s_out = s_dyn;
     load_camera(a, s_cam);
-    const int row0 = blockIdx.x * PB;
+    const int row0 = a.begin + blockIdx.x * PB;
     const int nrows = min(PB, a.P - row0);
     const int t = threadIdx.x;
     const int idx = row0 + t;
@@ -430,28 +441,42 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
         }
     }
     __syncthreads();                                    // SH rows are out: the same memory now stages the rest
+    const bool pack = a.small_pack != nullptr;
     if (valid) {
-        s_out[3 * t] = o.g[0]; s_out[3 * t + 1] = o.g[1]; s_out[3 * t + 2] = 0.f;
         reinterpret_cast<float4*>(s_out + 3 * PB)[t] = make_float4(o.g[2], o.g[3], 0.f, o.g[4]);
-        s_out[7 * PB + t] = o.g[5];
         s_out[8 * PB + 3 * t] = o.g[6]; s_out[8 * PB + 3 * t + 1] = o.g[7]; s_out[8 * PB + 3 * t + 2] = o.g[8];
-        s_out[11 * PB + 3 * t] = o.dmean[0]; s_out[11 * PB + 3 * t + 1] = o.dmean[1]; s_out[11 * PB + 3 * t + 2] = o.dmean[2];
 #pragma unroll
         for (int i = 0; i < 6; i++) s_out[14 * PB + 6 * t + i] = o.dcov[i];
-        s_out[20 * PB + 3 * t] = o.dscale[0]; s_out[20 * PB + 3 * t + 1] = o.dscale[1]; s_out[20 * PB + 3 * t + 2] = o.dscale[2];
-        reinterpret_cast<float4*>(s_out + 23 * PB)[t] = make_float4(o.drot[0], o.drot[1], o.drot[2], o.drot[3]);
         s_out[27 * PB + 3 * t] = o.drgb[0]; s_out[27 * PB + 3 * t + 1] = o.drgb[1]; s_out[27 * PB + 3 * t + 2] = o.drgb[2];
+        if (pack) {        // one 56-byte row per Gaussian; the rows use the 14*PB floats the five tensors' stages would
+            float* row = s_out + 30 * PB + 14 * t;
+            row[0] = o.dmean[0]; row[1] = o.dmean[1]; row[2] = o.dmean[2];
+            row[3] = o.g[0]; row[4] = o.g[1]; row[5] = 0.f;
+            row[6] = o.g[5];
+            row[7] = o.dscale[0]; row[8] = o.dscale[1]; row[9] = o.dscale[2];
+            row[10] = o.drot[0]; row[11] = o.drot[1]; row[12] = o.drot[2]; row[13] = o.drot[3];
+        } else {
+            s_out[3 * t] = o.g[0]; s_out[3 * t + 1] = o.g[1]; s_out[3 * t + 2] = 0.f;
+            s_out[7 * PB + t] = o.g[5];
+            s_out[11 * PB + 3 * t] = o.dmean[0]; s_out[11 * PB + 3 * t + 1] = o.dmean[1]; s_out[11 * PB + 3 * t + 2] = o.dmean[2];
+            s_out[20 * PB + 3 * t] = o.dscale[0]; s_out[20 * PB + 3 * t + 1] = o.dscale[1]; s_out[20 * PB + 3 * t + 2] = o.dscale[2];
+            reinterpret_cast<float4*>(s_out + 23 * PB)[t] = make_float4(o.drot[0], o.drot[1], o.drot[2], o.drot[3]);
+        }
     }
     __syncthreads();
-    copy_out(a.dL_dmean2D + (size_t)row0 * 3, s_out, nrows * 3);
     if (a.dL_dconic) copy_out(a.dL_dconic + (size_t)row0 * 4, s_out + 3 * PB, nrows * 4);
-    copy_out(a.dL_dopacity + row0, s_out + 7 * PB, nrows);
     copy_out(a.dL_dcolor + (size_t)row0 * 3, s_out + 8 * PB, nrows * 3);
-    copy_out(a.dL_dmean3D + (size_t)row0 * 3, s_out + 11 * PB, nrows * 3);
     copy_out(a.dL_dcov3D + (size_t)row0 * 6, s_out + 14 * PB, nrows * 6);
-    copy_out(a.dL_dscale + (size_t)row0 * 3, s_out + 20 * PB, nrows * 3);
-    copy_out(a.dL_drot + (size_t)row0 * 4, s_out + 23 * PB, nrows * 4);
     if (a.dL_drgb) copy_out(a.dL_drgb + (size_t)row0 * 3, s_out + 27 * PB, nrows * 3);
+    if (pack) {
+        copy_out(a.small_pack + (size_t)row0 * 14, s_out + 30 * PB, nrows * 14);
+    } else {
+        copy_out(a.dL_dmean2D + (size_t)row0 * 3, s_out, nrows * 3);
+        copy_out(a.dL_dopacity + row0, s_out + 7 * PB, nrows);
+        copy_out(a.dL_dmean3D + (size_t)row0 * 3, s_out + 11 * PB, nrows * 3);
+        copy_out(a.dL_dscale + (size_t)row0 * 3, s_out + 20 * PB, nrows * 3);
+        copy_out(a.dL_drot + (size_t)row0 * 4, s_out + 23 * PB, nrows * 4);
+    }
 }
 
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
@@ -463,13 +488,21 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     const bool aligned = (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0 &&
                          (reinterpret_cast<uintptr_t>(a.rotations) & 15) == 0;
     const bool staged = (L % 4 == 0) && aligned && dyn <= 40 * 1024 && (a.M == 0 || a.dL_dsh != nullptr);
-    static const int minb = getenv("GSR_PB_MINB") ? atoi(getenv("GSR_PB_MINB")) : 8;   // EXPERIMENT
-    if (staged && minb == 8) preprocess_bwd_kernel_staged<8><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
-    else if (staged && minb == 7) preprocess_bwd_kernel_staged<7><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
-    else if (staged && minb == 5) preprocess_bwd_kernel_staged<5><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
-    else if (staged) preprocess_bwd_kernel_staged<6><<<(a.P + PB - 1) / PB, PB, dyn, st>>>(a, S);
-    else preprocess_bwd_kernel_generic<<<(a.P + 255) / 256, 256, 0, st>>>(a);
-    count_launch(1);
+    // beside a collective (multi-view exchange): chunked, see chunk_plan
+    int bounds[5];
+    const int nchunk = a.chunked ? chunk_plan(a.P, 256, bounds) : 1;
+    if (nchunk == 1) { bounds[0] = 0; bounds[1] = a.P; }
+    for (int c = 0; c < nchunk; c++) {
+        PreprocessBwdArgs ac = a;
+        ac.begin = bounds[c]; ac.P = bounds[c + 1];
+        const int n = ac.P - ac.begin;
+        if (n <= 0) continue;
+        if (staged) preprocess_bwd_kernel_staged<8><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        else preprocess_bwd_kernel_generic<<<(n + 255) / 256, 256, 0, st>>>(ac);
+        count_launch(1);
+        if (a.chunk_events && c < a.n_chunk_events && c < nchunk - 1) cudaEventRecord((cudaEvent_t)a.chunk_events[c], st);
+    }
+    for (int c = nchunk - 1; a.chunk_events && c < a.n_chunk_events; c++) cudaEventRecord((cudaEvent_t)a.chunk_events[c], st);
 }
 
 }  // namespace gsr
@@ -506,7 +539,7 @@ __global__ void __launch_bounds__(MV) multiview_sh_grad_kernel(MultiviewShArgs a
     float* s_rgb = s_mv;
     float* s_rows = s_mv + a.n_views * MV * 3;
     __shared__ float s_campos[16 * 4];
-    const int row0 = blockIdx.x * MV;
+    const int row0 = a.begin + blockIdx.x * MV;
     const int nrows = min(MV, a.P - row0);
     const int t = threadIdx.x;
     if (t < a.n_views * 4) s_campos[t] = a.blocks[t >> 2][t & 3];
@@ -561,7 +594,7 @@ __global__ void __launch_bounds__(MV) multiview_sh_grad_kernel(MultiviewShArgs a
 
 // fallback for shapes the staged kernel does not take (3*M not a multiple of 4): one thread per Gaussian
 __global__ void __launch_bounds__(256) multiview_sh_grad_kernel_generic(MultiviewShArgs a) {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = a.begin + blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= a.P) return;
     float acc[48];
     for (int i = 0; i < 48; i++) acc[i] = 0.f;
@@ -599,6 +632,34 @@ __global__ void __launch_bounds__(256) publish_drgb_kernel(int P, const float* _
     for (int i = threadIdx.x; i < 768; i += 256) if (base + i < n) out[base + i] = s[i];
 }
 
+// rows [begin, end) of the (P,14) packed block -> the five gradient tensors, staged through shared memory so that both
+// sides are coalesced
+__global__ void __launch_bounds__(256) unpack_small_kernel(int begin, int end, const float* __restrict__ pack, float* __restrict__ dmean3D,
+                                                           float* __restrict__ dmean2D, float* __restrict__ dop, float* __restrict__ dscale,
+                                                           float* __restrict__ drot) {
+    __shared__ float s[256 * 14];
+    const int row0 = begin + blockIdx.x * 256;
+    const int nrows = min(256, end - row0);
+    const float* src = pack + (size_t)row0 * 14;
+    for (int i = threadIdx.x; i < nrows * 14; i += 256) s[i] = src[i];
+    __syncthreads();
+    for (int i = threadIdx.x; i < nrows * 3; i += 256) {
+        const int r = i / 3, c = i - 3 * r;
+        dmean3D[(size_t)row0 * 3 + i] = s[r * 14 + c];
+        dmean2D[(size_t)row0 * 3 + i] = s[r * 14 + 3 + c];
+        dscale[(size_t)row0 * 3 + i] = s[r * 14 + 7 + c];
+    }
+    for (int i = threadIdx.x; i < nrows; i += 256) dop[row0 + i] = s[i * 14 + 6];
+    for (int i = threadIdx.x; i < nrows * 4; i += 256) drot[(size_t)row0 * 4 + i] = s[(i >> 2) * 14 + 10 + (i & 3)];
+}
+
+void launch_unpack_small(int begin, int end, const float* pack, float* dmean3D, float* dmean2D, float* dop, float* dscale,
+                         float* drot, cudaStream_t st) {
+    if (end <= begin) return;
+    unpack_small_kernel<<<(end - begin + 255) / 256, 256, 0, st>>>(begin, end, pack, dmean3D, dmean2D, dop, dscale, drot);
+    count_launch(1);
+}
+
 void launch_publish_drgb(int P, const float* grad_acc, const int* radii, const uint8_t* clamped, float* out, cudaStream_t st) {
     if (P <= 0) return;
     publish_drgb_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, grad_acc, radii, clamped, out);
@@ -610,18 +671,27 @@ void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st) {
     const int L = 3 * a.M;
     const int S = ((L / 4) % 2 == 1) ? L : L + 4;
     const size_t dyn = ((size_t)a.n_views * MV * 3 + (size_t)MV * S) * sizeof(float);
-    if (L % 4 == 0 && dyn <= 44 * 1024) {
-        const unsigned grid = (a.P + MV - 1) / MV;
-        switch (a.D) {
-            case 0: multiview_sh_grad_kernel<0><<<grid, MV, dyn, st>>>(a, S); break;
-            case 1: multiview_sh_grad_kernel<1><<<grid, MV, dyn, st>>>(a, S); break;
-            case 2: multiview_sh_grad_kernel<2><<<grid, MV, dyn, st>>>(a, S); break;
-            default: multiview_sh_grad_kernel<3><<<grid, MV, dyn, st>>>(a, S); break;
+    // runs beside the all-reduce of the small gradients: chunked, see chunk_plan
+    int bounds[5];
+    const int nchunk = chunk_plan(a.P, 256, bounds);
+    for (int c = 0; c < nchunk; c++) {
+        MultiviewShArgs ac = a;
+        ac.begin = bounds[c]; ac.P = bounds[c + 1];
+        const int n = ac.P - ac.begin;
+        if (n <= 0) continue;
+        if (L % 4 == 0 && dyn <= 44 * 1024) {
+            const unsigned grid = (n + MV - 1) / MV;
+            switch (a.D) {
+                case 0: multiview_sh_grad_kernel<0><<<grid, MV, dyn, st>>>(ac, S); break;
+                case 1: multiview_sh_grad_kernel<1><<<grid, MV, dyn, st>>>(ac, S); break;
+                case 2: multiview_sh_grad_kernel<2><<<grid, MV, dyn, st>>>(ac, S); break;
+                default: multiview_sh_grad_kernel<3><<<grid, MV, dyn, st>>>(ac, S); break;
+            }
+        } else {
+            multiview_sh_grad_kernel_generic<<<(n + 255) / 256, 256, 0, st>>>(ac);
         }
-    } else {
-        multiview_sh_grad_kernel_generic<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+        count_launch(1);
     }
-    count_launch(1);
 }
 
 }  // namespace gsr

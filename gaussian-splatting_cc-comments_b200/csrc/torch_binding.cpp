@@ -88,7 +88,8 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
                                const torch::Tensor& campos, const torch::Tensor& geomBuffer, const int R,
                                const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const bool debug,
                                const int tile_row_begin, const int tile_row_end,
-                               const c10::optional<torch::Tensor>& drgb_block, const bool skip_dsh, const int64_t drgb_event) {
+                               const c10::optional<torch::Tensor>& drgb_block, const bool skip_dsh, const int64_t drgb_event,
+                               const std::vector<int64_t>& chunk_events, const c10::optional<torch::Tensor>& small_pack) {
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
     const c10::cuda::CUDAGuard guard(means3D.device());
     const auto dev = means3D.device();
@@ -139,6 +140,18 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
             a.dL_drgb = drgb_block->data_ptr<float>() + 4;
             a.skip_dL_dsh = skip_dsh ? 1 : 0;
             a.drgb_ready_event = reinterpret_cast<void*>(drgb_event);      // cudaEvent_t (torch.cuda.Event.cuda_event) or 0
+        }
+        void* chunk_ev[GSR_MAX_CHUNKS];
+        if (!chunk_events.empty()) {
+            TORCH_CHECK((int)chunk_events.size() <= GSR_MAX_CHUNKS, "at most ", GSR_MAX_CHUNKS, " chunk events");
+            for (size_t i = 0; i < chunk_events.size(); i++) chunk_ev[i] = reinterpret_cast<void*>(chunk_events[i]);
+            a.chunk_done_events = chunk_ev;
+            a.n_chunk_events = (int)chunk_events.size();
+        }
+        if (small_pack.has_value() && small_pack->numel() > 0) {      // (P,14) rows instead of the five small tensors
+            TORCH_CHECK(small_pack->scalar_type() == torch::kFloat32 && small_pack->is_contiguous() && small_pack->device() == dev &&
+                        small_pack->numel() >= GSR_SMALL_PACK_FLOATS * P, "small_pack must be a contiguous float32 tensor of >= 14P elements on ", dev);
+            a.small_pack = small_pack->data_ptr<float>();
         }
         cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
         check(gsr_backward(&a, (void*)st));
@@ -203,7 +216,30 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("dL_dout_color"), py::arg("sh"), py::arg("degree"), py::arg("campos"), py::arg("geomBuffer"), py::arg("R"),
           py::arg("binningBuffer"), py::arg("imageBuffer"), py::arg("debug"), py::arg("tile_row_begin") = 0,
           py::arg("tile_row_end") = 0, py::arg("drgb_block") = py::none(), py::arg("skip_dsh") = false,
-          py::arg("drgb_event") = 0);
+          py::arg("drgb_event") = 0, py::arg("chunk_events") = std::vector<int64_t>(),
+          py::arg("small_pack") = py::none());
+    m.def("unpack_small_grads", [](int64_t begin, int64_t end, const torch::Tensor& pack, torch::Tensor& dmean3D, torch::Tensor& dmean2D,
+                                   torch::Tensor& dop, torch::Tensor& dscale, torch::Tensor& drot) {
+        TORCH_CHECK(pack.is_cuda() && pack.is_contiguous() && pack.scalar_type() == torch::kFloat32, "pack: contiguous float32 CUDA tensor");
+        for (const torch::Tensor* t : {&dmean3D, &dmean2D, &dop, &dscale, &drot})
+            TORCH_CHECK(t->is_cuda() && t->is_contiguous() && t->scalar_type() == torch::kFloat32 && t->device() == pack.device(),
+                        "gradient tensors: contiguous float32 on the pack's device");
+        TORCH_CHECK(end <= dmean3D.size(0) && GSR_SMALL_PACK_FLOATS * end <= pack.numel(), "range exceeds the tensors");
+        const c10::cuda::CUDAGuard guard(pack.device());
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(pack.device().index()).stream();
+        check(gsr_unpack_small_grads((int)begin, (int)end, pack.data_ptr<float>(), dmean3D.data_ptr<float>(), dmean2D.data_ptr<float>(),
+                                     dop.data_ptr<float>(), dscale.data_ptr<float>(), drot.data_ptr<float>(), (void*)st));
+    }, "rows [begin,end) of a (P,14) small_pack block -> the five gradient tensors (include/gsr.h)");
+    m.def("multimem_allreduce", [](int64_t mc_ptr, int64_t begin, int64_t end, int64_t rank, int64_t world, int64_t device) {
+        const c10::cuda::CUDAGuard guard(c10::Device(c10::kCUDA, (c10::DeviceIndex)device));
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)device).stream();
+        check(gsr_multimem_allreduce(reinterpret_cast<void*>(mc_ptr), (size_t)begin, (size_t)end, (int)rank, (int)world, (void*)st));
+    }, "two-shot all-reduce of floats [begin,end) through an NVLS multicast address (include/gsr.h)");
+    m.def("backward_chunk_plan", [](int64_t P) {
+        int b[GSR_MAX_CHUNKS + 1];
+        const int n = gsr_backward_chunk_plan((int)P, b);
+        return std::vector<int64_t>(b, b + n + 1);
+    }, "Gaussian ranges of the chunked per-Gaussian backward (include/gsr.h: gsr_backward_chunk_plan)");
     m.def("multiview_sh_grad", &multiviewShGrad);
     m.def("mark_visible", &markVisible);
     m.def("view_buffers", &viewBuffers);

@@ -17,6 +17,8 @@ drop-in API and does not change it.
 """
 from typing import List, NamedTuple, Optional, Sequence, Tuple
 
+import os
+import sys
 import torch
 import torch.distributed as dist
 
@@ -217,6 +219,8 @@ class MultiViewExchange:
         self.world = dist.get_world_size(self.group)
         self.rank = dist.get_rank(self.group)
         self.device = torch.device(device)
+        if self.device.index is None:
+            self.device = torch.device("cuda", torch.cuda.current_device())
         # how the 12 B/Gaussian blocks travel: "allgather" (default) = NCCL all-gather into local staging, then the SH
         # kernel on local data; "peer" = plain peer loads inside the SH kernel (symmetric memory).  Measured on 8 B200:
         # 5.18 vs 5.36 ms per step (profiles/r01_multigpu_c5.md) -- the all-gather goes through NVLS.
@@ -226,16 +230,68 @@ class MultiViewExchange:
         # short blocks, launched earlier) is running, not after it.  For the NCCL part set TORCH_NCCL_HIGH_PRIORITY=1
         # before init_process_group (bench.py does).
         self.side = torch.cuda.Stream(device=self.device, priority=-1)
+        # one level above the side stream: the reduction's small CTAs must not queue behind the SH kernel's blocks
+        self.comm = torch.cuda.Stream(device=self.device, priority=-2)
         self.ev_drgb = torch.cuda.Event()
         self.ev_done = torch.cuda.Event()
+        self.ev_small = torch.cuda.Event()
+        self.ev_ag = torch.cuda.Event()
+        self.ev_chunk = [torch.cuda.Event() for _ in range(4)]     # GSR_MAX_CHUNKS
         with torch.cuda.device(self.device):
             self.ev_drgb.record()                 # torch creates the cudaEvent lazily; the C ABI needs the handle
             self.ev_done.record()
+            self.ev_small.record()
+            self.ev_ag.record()
+            for e in self.ev_chunk:
+                e.record()
+        # GSR_MV_TIMELINE=1: timed events around every phase of the exchange (diagnostics; see timeline_report)
+        self._tl = [] if os.environ.get("GSR_MV_TIMELINE") == "1" else None
+        self._tl_cur = None
         self._alloc(int(capacity))
+
+    def _mark(self, name, stream=None):
+        if self._tl_cur is not None:
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(stream if stream is not None else torch.cuda.current_stream(self.device))
+            self._tl_cur.append((name, e))
+
+    def timeline_report(self, skip=5):
+        """Mean offsets (ms) of each phase boundary from the start of the backward, over the recorded steps."""
+        if not self._tl:
+            return {}
+        torch.cuda.synchronize(self.device)
+        acc = {}
+        for marks in self._tl[skip:]:
+            t0 = marks[0][1]
+            for name, e in marks[1:]:
+                acc.setdefault(name, []).append(t0.elapsed_time(e))
+        return {k: sum(v) / len(v) for k, v in acc.items()}
 
     def _alloc(self, capacity):
         self.capacity = capacity
         n = 4 + 3 * capacity
+        # (P,14) small-gradient rows.  "multimem": symmetric allocation bound to an NVLS multicast address, summed by
+        # this package's own two-shot kernel through the switch (gsr_multimem_allreduce); "nccl": plain tensor, NCCL
+        # all-reduce of each range.  multimem needs NVSwitch multicast support; it falls back by itself (collectively:
+        # every rank sees the same answer from the rendezvous).
+        self.pack_handle, self.pack_mc = None, 0
+        # Default "nccl": on 8 B200 the multimem kernel of this round needs 0.3-0.4 ms for its 21 MB slice and the step
+        # ends later (4.34 ms vs 4.01 ms, profiles/r01_multigpu_c5.md); it stays selectable for the next round's work.
+        want = os.environ.get("GSR_MULTIVIEW_SMALL", "nccl")
+        if want == "multimem":
+            try:
+                self.pack = self._symm.empty(14 * capacity, dtype=torch.float32, device=self.device)
+                self.pack.zero_()
+                self.pack_handle = self._symm.rendezvous(self.pack, self.group)
+                self.pack_mc = int(getattr(self.pack_handle, "multicast_ptr", 0) or 0)
+            except Exception as e:      # no symmetric memory / no multicast on this machine
+                self.pack_handle, self.pack_mc = None, 0
+                if self.rank == 0:
+                    print("gsr_multi_gpu: multimem exchange unavailable (%s); using NCCL for the small gradients" % (e,), file=sys.stderr)
+        if not self.pack_mc:
+            self.pack_handle = None
+            self.pack = torch.zeros(14 * capacity, dtype=torch.float32, device=self.device)
+        self.small_mode = "multimem" if self.pack_mc else "nccl"
         if self.mode == "allgather":
             self.block = torch.zeros(n, dtype=torch.float32, device=self.device)
             self.stage = torch.zeros(self.world * n, dtype=torch.float32, device=self.device)
@@ -252,7 +308,12 @@ class MultiViewExchange:
         if P > self.capacity:                     # densification grew the model: same P on every rank, so this is collective
             self._alloc(int(P * 1.25) + 1024)
         self.block[:3].copy_(campos.reshape(-1)[:3], non_blocking=True)
-        return self.block, True, int(self.ev_drgb.cuda_event)
+        if self._tl is not None:
+            self._tl_cur = []
+            self._tl.append(self._tl_cur)
+            self._mark("backward_start")
+        return (self.block, True, int(self.ev_drgb.cuda_event), [int(e.cuda_event) for e in self.ev_chunk],
+                self.pack if self.small_mode == "multimem" else None)
 
     def exchange(self, C, means3D, sh_degree, grad_sh, small_grads):
         P = means3D.shape[0]
@@ -260,27 +321,58 @@ class MultiViewExchange:
         main = torch.cuda.current_stream(self.device)
         # side stream: starts as soon as dL/dRGB is published (event recorded by gsr_backward right after the blending
         # backward), i.e. it runs beside the per-Gaussian backward that the main stream is still executing
+        self._mark("per_gaussian_backward_done", main)
         self.side.wait_event(self.ev_drgb)
         with torch.cuda.stream(self.side):
+            self._mark("drgb_published", self.side)
             if self.mode == "allgather":
                 out = self.stage[: self.world * n]
                 dist.all_gather_into_tensor(out, self.block[:n], group=self.group)
+                self.ev_ag.record(self.side)
+                self._mark("allgather_done", self.side)
                 ptrs = [out[r * n:].data_ptr() for r in range(self.world)]
                 C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
+                self._mark("sh_kernel_done", self.side)
             else:
                 self.handle.barrier(channel=0)    # every rank's dL/dRGB and campos are in place
+                self.ev_ag.record(self.side)
                 # start with the next rank's block so that the ranks do not all pull from the same GPU at once
                 ptrs = [self.peer_ptrs[(self.rank + 1 + i) % self.world] for i in range(self.world)]
                 C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
                 self.handle.barrier(channel=1)    # nobody overwrites a block a peer is still reading
             self.ev_done.record(self.side)
-        span = flat_span(small_grads)             # main stream: ordered after the per-Gaussian backward
-        if span is not None:
-            dist.all_reduce(span, op=dist.ReduceOp.SUM, group=self.group)
+        # The 14 other live floats per Gaussian.  The links carry one thing at a time: first the all-gather above (it
+        # gates the SH kernel, the longest tail), then this sum -- measured on 8 B200, running both at once doubles the
+        # all-gather's time and the step ends later (profiles/r01_multigpu_c5.md).
+        g3d, g2d, gop, gsc, grot = small_grads
+        if self.small_mode == "multimem":
+            # rows of the symmetric (P,14) block, summed through the switch by this package's own kernel
+            # (multimem.ld_reduce + multimem.st on this rank's 1/world slice), then scattered into the five tensors
+            self.comm.wait_event(self.ev_ag)
+            self.comm.wait_event(self.ev_chunk[-1])          # the per-Gaussian backward has written every row
+            with torch.cuda.stream(self.comm):
+                self._mark("small_start", self.comm)
+                self.pack_handle.barrier(channel=2)          # ... on every rank
+                self._mark("small_barrier_in", self.comm)
+                C.multimem_allreduce(self.pack_mc, 0, 14 * int(P), self.rank, self.world, self.device.index)
+                self._mark("small_reduced", self.comm)
+                self.pack_handle.barrier(channel=3)          # every rank's slice is reduced and broadcast
+                self._mark("small_barrier_out", self.comm)
+                C.unpack_small_grads(0, int(P), self.pack, g3d, g2d, gop, gsc, grot)
+            self.ev_small.record(self.comm)
+            main.wait_event(self.ev_small)
         else:
-            for g in small_grads:
-                dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
+            # NCCL: one all-reduce of the contiguous small block of the gradient arena, on the main stream (ordered
+            # after the per-Gaussian backward; NCCL runs it behind the all-gather on its own stream)
+            span = flat_span(small_grads)
+            if span is not None:
+                dist.all_reduce(span, op=dist.ReduceOp.SUM, group=self.group)
+            else:
+                for g in small_grads:
+                    dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
+        self._mark("allreduce_done", main)
         main.wait_event(self.ev_done)
+        self._mark("exchange_done", main)
 
 
 def enable_multiview_training(capacity, device, group=None, mode=None):

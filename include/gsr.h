@@ -118,7 +118,25 @@ typedef struct gsr_backward_args {
      * backward, BEFORE the per-Gaussian backward runs -- so that the exchange of dL_drgb between ranks can
      * overlap with the rest of this call.  NULL = no event. */
     void* drgb_ready_event;
+    /* Optional cudaEvent_t handles (n_chunk_events of them, at most GSR_MAX_CHUNKS).  With dL_drgb set the
+     * per-Gaussian backward runs as gsr_backward_chunk_plan(P) consecutive launches over ranges of Gaussians and
+     * chunk_done_events[c] is recorded on the stream after range c (handles beyond the number of ranges are
+     * recorded after the last one): the caller can reduce a range's gradients across ranks while the later
+     * ranges are still being computed.  NULL / 0 = no events. */
+    void* const* chunk_done_events;
+    int n_chunk_events;
+    /* Optional (P,14) row-major block.  When set, the five small live gradients of a Gaussian -- dL_dmean3D (3),
+     * dL_dmean2D (3), dL_dopacity (1), dL_dscale (3), dL_drot (4), in this order -- are written there as ONE
+     * 56-byte row INSTEAD of into their five tensors, so that a range of Gaussians is one contiguous span for
+     * the cross-rank reduction; gsr_unpack_small_grads then scatters reduced rows into the five tensors. */
+    float* small_pack;
 } gsr_backward_args;
+#define GSR_SMALL_PACK_FLOATS 14
+
+/* The ranges of Gaussians the chunked per-Gaussian backward uses for P Gaussians: bounds[0] = 0 <= ... <=
+ * bounds[n] = P, n returned (1..GSR_MAX_CHUNKS); bounds needs GSR_MAX_CHUNKS + 1 ints. */
+#define GSR_MAX_CHUNKS 4
+int gsr_backward_chunk_plan(int P, int* bounds);
 
 /* Bytes needed for gsr_backward_args.grad_scratch */
 size_t gsr_backward_scratch_bytes(int P);
@@ -145,6 +163,17 @@ int gsr_backward(const gsr_backward_args* args, void* cuda_stream);
 #define GSR_MAX_VIEWS 16
 int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* peer_blocks, const float* means3D,
                           float* dL_dsh, void* cuda_stream);
+
+/* Rows [begin, end) of a (P,14) small_pack block -> the five gradient tensors (see gsr_backward_args.small_pack). */
+int gsr_unpack_small_grads(int begin, int end, const float* small_pack, float* dL_dmean3D, float* dL_dmean2D,
+                           float* dL_dopacity, float* dL_dscale, float* dL_drot, void* cuda_stream);
+
+/* Sum over `world` ranks of floats [begin, end) of a buffer that every rank allocated symmetrically and bound to one
+ * NVLS multicast address (`multicast_base`, 16-byte aligned; begin a multiple of 4): this rank reduces its 1/world
+ * slice through the switch (multimem.ld_reduce) and broadcasts it into every rank's copy (multimem.st).  Collective:
+ * every rank launches it with the same range; the caller places a device barrier before (all ranks' data written) and
+ * after (all slices broadcast).  No reference counterpart (multi-view training extension). */
+int gsr_multimem_allreduce(void* multicast_base, size_t begin, size_t end, int rank, int world, void* cuda_stream);
 
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      unsigned char* present /* (P) bool out */, void* cuda_stream);

@@ -273,3 +273,43 @@ def test_multiview_sh_gradient_kernel_equals_sum_of_single_view_gradients(mod):
         K = (deg + 1) ** 2
         assert Hh.rel_l2(out[:, :K].cpu().numpy(), ref_sum[:, :K].cpu().numpy()) <= 1e-5
         assert float(out[:, K:].abs().max()) == 0.0 if K < 16 else True
+
+
+def test_chunked_backward_with_packed_small_gradients_matches_plain_backward(mod):
+    """Multi-view exchange plumbing on ONE GPU: the per-Gaussian backward launched in ranges (gsr_backward_chunk_plan),
+    one event per range, the 14 small floats written as (P,14) rows and scattered back by gsr_unpack_small_grads --
+    every gradient must match the plain single-launch backward."""
+    import torch
+    P, W, H = 150000, 320, 200
+    cam = S.make_camera(W, H)
+    scene = S.make_scene(P, cam, sh_degree=3, M=16, seed=9, s0_pix=1.5)
+    t = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32, device="cuda")
+    dL = t(S.upstream_grad(cam, seed=21))
+    st = mod.GaussianRasterizationSettings(H, W, cam["tanfovx"], cam["tanfovy"], t([0.1, 0.2, 0.3]), 1.0, t(cam["viewmatrix"]),
+                                           t(cam["projmatrix"]), 3, t(cam["campos"]), False, False)
+    m3, sh, op, sc, rot = t(scene["means3D"]), t(scene["shs"]), t(scene["opacities"]), t(scene["scales"]), t(scene["rotations"])
+    e = torch.Tensor([])
+    nr, color, radii, gb, bb, ib = mod._C.rasterize_gaussians(st.bg, m3, e, op, sc, rot, 1.0, e, st.viewmatrix, st.projmatrix, st.tanfovx,
+                                                              st.tanfovy, H, W, sh, 3, st.campos, False, False)
+    bargs = (st.bg, m3, radii, e, sc, rot, 1.0, e, st.viewmatrix, st.projmatrix, st.tanfovx, st.tanfovy, dL, sh, 3, st.campos,
+             gb, nr, bb, ib, False)
+    plain = mod._C.rasterize_gaussians_backward(*bargs)
+    bounds = [int(b) for b in mod._C.backward_chunk_plan(P)]
+    assert bounds[0] == 0 and bounds[-1] == P and len(bounds) == 5 and all(b1 >= b0 for b0, b1 in zip(bounds, bounds[1:]))
+    assert [int(b) for b in mod._C.backward_chunk_plan(1000)] == [0, 1000]
+    blk = torch.zeros(4 + 3 * P, device="cuda")
+    evs = [torch.cuda.Event() for _ in range(5)]
+    for ev in evs:
+        ev.record()
+    pack = torch.full((14 * P,), 5.0, device="cuda")
+    fused = mod._C.rasterize_gaussians_backward(*bargs, 0, 0, blk, False, int(evs[0].cuda_event), [int(ev.cuda_event) for ev in evs[1:]], pack)
+    side = torch.cuda.Stream()
+    g2d, gcol, gop, g3d, gcov, gsh, gsc, grot = fused
+    for c in range(4):                     # consume each range as soon as its event fires, on another stream
+        side.wait_event(evs[1 + c])
+        with torch.cuda.stream(side):
+            mod._C.unpack_small_grads(bounds[c], bounds[c + 1], pack, g3d, g2d, gop, gsc, grot)
+    torch.cuda.synchronize()
+    # the blending backward sums with float atomics, so two runs agree to rounding, not bitwise
+    for a, b, name in zip(plain, fused, ("means2D", "colors", "opacity", "means3D", "cov3D", "sh", "scales", "rotations")):
+        assert Hh.rel_l2(b.cpu().numpy(), a.cpu().numpy()) <= 1e-5, name
