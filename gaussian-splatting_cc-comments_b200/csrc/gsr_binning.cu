@@ -13,7 +13,6 @@
 // Stability of (2) keeps depth order (and index order among equal depths) inside each tile.
 // All of it is HBM-bound integer work: coalesced key loads, warp-level match_any ranking in
 // shared memory, no tensor cores.
-#include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
 
@@ -324,19 +323,10 @@ __global__ void __launch_bounds__(RS_THREADS, RS_MINB) rs_sweep_kernel(const uin
 // Stable LSD sort of n (key, value) pairs on the given digit passes; input in keys[s0]/vals[s0], the result ends
 // in keys[s0 ^ (npass & 1)].  `table` (rs_table_words(n) words) holds the digit histograms of all passes
 // [p*256, p*256+256), the ticket counters [1024 + p] and one look-back table per pass from word 1280.
-template <bool BALLOT>
-static void launch_sweep(int items, unsigned nb, cudaStream_t st, const uint32_t* kin, const uint32_t* vin, uint32_t* kout, uint32_t* vout,
-                         size_t n, int shift, int bits, const uint32_t* ghist, uint32_t* ticket, uint32_t* lookback) {
-    if (items == 8) rs_sweep_kernel<BALLOT, 8><<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, ghist, ticket, lookback);
-    else if (items == 12) rs_sweep_kernel<BALLOT, 12><<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, ghist, ticket, lookback);
-    else rs_sweep_kernel<BALLOT, 16><<<nb, RS_THREADS, 0, st>>>(kin, vin, kout, vout, n, shift, bits, ghist, ticket, lookback);
-}
-
 void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, size_t n, int npass, const int* shifts,
-                    const int* bits, uint32_t* table, int items, cudaStream_t st) {
+                    const int* bits, uint32_t* table, cudaStream_t st) {
     if (n == 0 || npass <= 0) return;
-    if (items != 8 && items != 12) items = 16;
-    const unsigned nb = (unsigned)((n + (size_t)RS_THREADS * items - 1) / ((size_t)RS_THREADS * items));
+    const unsigned nb = (unsigned)rs_blocks(n);
     cudaMemsetAsync(table, 0, (1280 + (size_t)npass * nb * RS_BINS) * sizeof(uint32_t), st);
     RsPasses ps;
     ps.n = npass;
@@ -351,12 +341,13 @@ void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, si
     int s = s0;
     for (int p = 0; p < npass; p++) {
         // digits of fewer than 8 bits (the two tile-id passes): per-bit ballots beat match.any; measured on B200
+        // (tiles of 8 or 12 items per thread measured slower than 16 for both sorts)
         if (bits[p] < 8)
-            launch_sweep<true>(items, nb, st, keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
-                               table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
+            rs_sweep_kernel<true, RS_ITEMS><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
+                                                                       table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
         else
-            launch_sweep<false>(items, nb, st, keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
-                                table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
+            rs_sweep_kernel<false, RS_ITEMS><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
+                                                                        table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
         s ^= 1;
     }
     count_launch(1 + npass);
@@ -448,8 +439,7 @@ void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, con
                       const float4* packed, const int* radii, int grid_x, int grid_y, int row_begin, int row_end,
                       uint32_t* tile_keys, uint32_t* vals, cudaStream_t st) {
     if (P <= 0) return;
-    static const bool coop = !(getenv("GSR_DUP_COOP") && atoi(getenv("GSR_DUP_COOP")) == 0);   // EXPERIMENT
-    if (coop && grid_x < 65536 && grid_y < 65536)
+    if (grid_x < 65536 && grid_y < 65536)       // measured 0.111 -> 0.075 ms at C2 against the one-thread-per-Gaussian walk
         duplicate_coop_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
                                                                row_begin, row_end, tile_keys, vals);
     else

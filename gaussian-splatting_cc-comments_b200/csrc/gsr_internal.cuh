@@ -45,8 +45,7 @@ constexpr int SCAN_THREADS = 512;
 constexpr int SCAN_ITEMS = 8;
 constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // 4096
 
-constexpr int RS_MIN_TILE = RS_THREADS * 8;       // smallest tile a pass may use: sizes the look-back tables
-static inline size_t rs_blocks(size_t n) { return (n + RS_MIN_TILE - 1) / RS_MIN_TILE; }
+static inline size_t rs_blocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
 static inline size_t rs_table_words(size_t n) { return 1280 + 4 * rs_blocks(n) * RS_BINS; }   // see radix_sort_u32
 static inline size_t scan_blocks(size_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
 
@@ -146,7 +145,7 @@ void scan_exclusive_u32(const uint32_t* in, uint32_t* out, size_t n, uint32_t* t
 
 // stable LSD radix sort on up to 4 digit passes (bits[p] <= 8 key bits starting at shifts[p]); see gsr_binning.cu
 void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, size_t n, int npass, const int* shifts,
-                    const int* bits, uint32_t* table, int items_per_thread, cudaStream_t st);
+                    const int* bits, uint32_t* table, cudaStream_t st);
 
 void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, size_t n, cudaStream_t st);
 

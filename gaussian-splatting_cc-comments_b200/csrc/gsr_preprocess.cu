@@ -10,7 +10,6 @@
 //     (3 x st.v4) instead of five separate arrays, plus conservative cull extents,
 //   * cov3D is not stored (the backward recomputes it from scale/rotation),
 //   * the depth-sort key/value pair is emitted here.
-#include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
 #include <stdio.h>
@@ -46,8 +45,8 @@ __device__ __forceinline__ void sh_color_scalar(int K, const float* __restrict__
         for (int ch = 0; ch < 3; ch++) res[ch] = fmar(k[kk], __ldg(sh + 3 * kk + ch), res[ch]);
 }
 
-template <int MINB>
-__global__ void __launch_bounds__(256, MINB) preprocess_fwd_kernel(PreprocessArgs a) {
+// 4 blocks per SM (64 registers): measured 0.194 -> 0.170 ms at C2 against the 85-register build
+__global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a) {
     __shared__ float s_cam[36];
     if (threadIdx.x < 16) s_cam[threadIdx.x] = a.cam.view[threadIdx.x];
     else if (threadIdx.x < 32) s_cam[threadIdx.x] = a.cam.proj[threadIdx.x - 16];
@@ -195,10 +194,7 @@ __global__ void __launch_bounds__(256, MINB) preprocess_fwd_kernel(PreprocessArg
 
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
-    static const int minb = getenv("GSR_PF_MINB") ? atoi(getenv("GSR_PF_MINB")) : 4;   // EXPERIMENT
-    if (minb == 4) preprocess_fwd_kernel<4><<<(a.P + 255) / 256, 256, 0, st>>>(a);
-    else if (minb == 5) preprocess_fwd_kernel<5><<<(a.P + 255) / 256, 256, 0, st>>>(a);
-    else preprocess_fwd_kernel<2><<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
     count_launch(1);
 }
 

@@ -382,7 +382,7 @@ __device__ __forceinline__ void copy_out(float* __restrict__ dst, const float* _
     for (int i = 4 * n4 + threadIdx.x; i < n; i += PB) dst[i] = src[i];
 }
 
-template <int MINB>
+template <int MINB, bool PACK>
 __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(PreprocessBwdArgs a, int S /* smem row stride, floats */) {
     __shared__ float s_cam[36];
     __shared__ uint8_t s_vis[PB];
@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
         }
     }
     __syncthreads();                                    // SH rows are out: the same memory now stages the rest
-    const bool pack = a.small_pack != nullptr;
+    constexpr bool pack = PACK;        // compile-time: the single-GPU instantiation is untouched by the exchange layout
     if (valid) {
         reinterpret_cast<float4*>(s_out + 3 * PB)[t] = make_float4(o.g[2], o.g[3], 0.f, o.g[4]);
         s_out[8 * PB + 3 * t] = o.g[6]; s_out[8 * PB + 3 * t + 1] = o.g[7]; s_out[8 * PB + 3 * t + 2] = o.g[8];
@@ -497,7 +497,8 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
         ac.begin = bounds[c]; ac.P = bounds[c + 1];
         const int n = ac.P - ac.begin;
         if (n <= 0) continue;
-        if (staged) preprocess_bwd_kernel_staged<8><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        if (staged && a.small_pack) preprocess_bwd_kernel_staged<8, true><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        else if (staged) preprocess_bwd_kernel_staged<8, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
         else preprocess_bwd_kernel_generic<<<(n + 255) / 256, 256, 0, st>>>(ac);
         count_launch(1);
         if (a.chunk_events && c < a.n_chunk_events && c < nchunk - 1) cudaEventRecord((cudaEvent_t)a.chunk_events[c], st);

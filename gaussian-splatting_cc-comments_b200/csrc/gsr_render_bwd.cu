@@ -12,7 +12,6 @@
 //     that the preprocess backward consumes;
 // Per-pixel replay order (the T division chain, backward.cu:534) is unchanged; only the
 // cross-pixel summation order differs (gradient tolerance 1e-4 relative L2).
-#include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
 #include "gsr_smem.cuh"
@@ -33,7 +32,7 @@ __device__ __forceinline__ void reduce_scatter_step(float* v, int bit, bool uppe
     }
 }
 
-template <bool PRED>
+// 5 blocks per SM: 6 and 8 measured slower (1.408 / 1.395 vs 1.360 ms at C2)
 __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
                                                          int W, int H, int grid_x, int row_begin,
                                                          const float4* __restrict__ packed, const float* __restrict__ bg,
@@ -114,114 +113,50 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
                 const int pos = first_pos - j;
                 const uint32_t ja = sb + (uint32_t)j * 16;
                 float v[8];
-                float v8 = 0.f;
-                if (PRED) {
-                    // Branch-free replay: the forward's warp mask guarantees at least one contributing lane, so every
-                    // instruction below issues anyway; lanes that do not contribute run with alpha = G = 0, which
-                    // leaves T (x 1/(1-0)), the accum_rec recurrence (0*c + 1*rec) and all nine sums unchanged.
-                    const float4 a = lds128<0>(ja);
-                    const float4 b = lds128<BOFF_B>(ja);
-                    const float2 gb = lds64<BOFF_C>(ja);
-                    const float dx = subr(a.x, pixfx), dy = subr(a.y, pixfy);
-                    const float s = fmar(dx, mulr(dx, a.z), mulr(dy, mulr(dy, b.x)));
-                    const float power = fmar(s, -0.5f, -mulr(dy, mulr(dx, a.w)));
-                    const float G0 = expf(power);
-                    const float alpha0 = fminf(0.99f, mulr(b.z, G0));
-                    const bool c = (pos < last_contributor) && !(power > 0.0f) && !(power < b.y) && !(alpha0 < 1.0f / 255.0f);
-                    const float alpha = c ? alpha0 : 0.0f;
-                    const float G = c ? G0 : 0.0f;
-                    float inv;
-                    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(1.0f - alpha));
-                    T = T * inv;
-                    const float dchannel_dcolor = alpha * T;
-                    ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0;
-                    ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1;
-                    ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2;
-                    lc0 = b.w; lc1 = gb.x; lc2 = gb.y;
-                    float dL_dalpha = (lc0 - ar0) * dpix0 + (lc1 - ar1) * dpix1 + (lc2 - ar2) * dpix2;
-                    v[6] = dchannel_dcolor * dpix0;
-                    v[7] = dchannel_dcolor * dpix1;
-                    v8 = dchannel_dcolor * dpix2;
-                    dL_dalpha *= T;
-                    last_alpha = alpha;
-                    dL_dalpha += (-T_final * inv) * bg_dot_dpixel;
-                    const float w = (b.z * dL_dalpha) * G;
-                    const float wx = w * dx, wy = w * dy;
-                    v[0] = wx; v[1] = wy; v[2] = wx * dx; v[3] = wx * dy; v[4] = wy * dy;
-                    v[5] = G * dL_dalpha;
-                    reduce_scatter_step<8>(v, 16, (lane & 16) != 0);
-                    reduce_scatter_step<4>(v, 8, (lane & 8) != 0);
-                    reduce_scatter_step<2>(v, 4, (lane & 4) != 0);
-                    float r = v[0];
-                    r += __shfl_xor_sync(0xffffffffu, r, 2);
-                    r += __shfl_xor_sync(0xffffffffu, r, 1);
+                float v8;
+                // Branch-free replay: the forward's warp mask guarantees at least one contributing lane, so every
+                // instruction below issues anyway; lanes that do not contribute run with alpha = G = 0, which
+                // leaves T (x 1/(1-0)), the accum_rec recurrence (0*c + 1*rec) and all nine sums unchanged.
+                const float4 a = lds128<0>(ja);
+                const float4 b = lds128<BOFF_B>(ja);
+                const float2 gb = lds64<BOFF_C>(ja);
+                const float dx = subr(a.x, pixfx), dy = subr(a.y, pixfy);
+                const float s = fmar(dx, mulr(dx, a.z), mulr(dy, mulr(dy, b.x)));
+                const float power = fmar(s, -0.5f, -mulr(dy, mulr(dx, a.w)));
+                const float G0 = expf(power);
+                const float alpha0 = fminf(0.99f, mulr(b.z, G0));
+                const bool c = (pos < last_contributor) && !(power > 0.0f) && !(power < b.y) && !(alpha0 < 1.0f / 255.0f);
+                const float alpha = c ? alpha0 : 0.0f;
+                const float G = c ? G0 : 0.0f;
+                float inv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(1.0f - alpha));
+                T = T * inv;
+                const float dchannel_dcolor = alpha * T;
+                ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0;
+                ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1;
+                ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2;
+                lc0 = b.w; lc1 = gb.x; lc2 = gb.y;
+                float dL_dalpha = (lc0 - ar0) * dpix0 + (lc1 - ar1) * dpix1 + (lc2 - ar2) * dpix2;
+                v[6] = dchannel_dcolor * dpix0;
+                v[7] = dchannel_dcolor * dpix1;
+                v8 = dchannel_dcolor * dpix2;
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final * inv) * bg_dot_dpixel;
+                const float w = (b.z * dL_dalpha) * G;
+                const float wx = w * dx, wy = w * dy;
+                v[0] = wx; v[1] = wy; v[2] = wx * dx; v[3] = wx * dy; v[4] = wy * dy;
+                v[5] = G * dL_dalpha;
+                reduce_scatter_step<8>(v, 16, (lane & 16) != 0);
+                reduce_scatter_step<4>(v, 8, (lane & 8) != 0);
+                reduce_scatter_step<2>(v, 4, (lane & 4) != 0);
+                float r = v[0];
+                r += __shfl_xor_sync(0xffffffffu, r, 2);
+                r += __shfl_xor_sync(0xffffffffu, r, 1);
 #pragma unroll
-                    for (int d = 16; d > 0; d >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, d);
-                    float* dst = grad_acc + 12 * (size_t)lds32u<BOFF_ID>(sb + (uint32_t)j * 4);
-                    if (red_lane) atomicAdd(dst + red_idx, lane == 1 ? v8 : r);
-                    continue;
-                }
-#pragma unroll
-                for (int q = 0; q < 8; q++) v[q] = 0.f;
-                bool contrib = false;
-                if (pos < last_contributor) {
-                    const float4 a = lds128<0>(ja);         // x, y, conic.x, conic.y
-                    const float4 b = lds128<BOFF_B>(ja);    // conic.z, power_thr, opacity, r
-                    // same expression as the forward, so the same pairs pass the tests
-                    const float dx = subr(a.x, pixfx), dy = subr(a.y, pixfy);
-                    const float s = fmar(dx, mulr(dx, a.z), mulr(dy, mulr(dy, b.x)));
-                    const float power = fmar(s, -0.5f, -mulr(dy, mulr(dx, a.w)));
-                    if (!(power > 0.0f) && !(power < b.y)) {
-                        const float G = expf(power);
-                        const float alpha = fminf(0.99f, mulr(b.z, G));
-                        if (!(alpha < 1.0f / 255.0f)) {
-                            contrib = true;
-                            const float2 gb = lds64<BOFF_C>(ja);   // g, b
-                            const float one_m_alpha = 1.0f - alpha;
-                            float inv;                                     // 1 - alpha >= 0.01: MUFU.RCP (1 ulp) is enough here
-                            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(one_m_alpha));
-                            T = T * inv;                                   // backward.cu:534
-                            const float dchannel_dcolor = alpha * T;
-                            // backward.cu:542-562
-                            ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0;
-                            ar1 = last_alpha * lc1 + (1.f - last_alpha) * ar1;
-                            ar2 = last_alpha * lc2 + (1.f - last_alpha) * ar2;
-                            lc0 = b.w; lc1 = gb.x; lc2 = gb.y;
-                            float dL_dalpha = (lc0 - ar0) * dpix0 + (lc1 - ar1) * dpix1 + (lc2 - ar2) * dpix2;
-                            v[6] = dchannel_dcolor * dpix0;
-                            v[7] = dchannel_dcolor * dpix1;
-                            v8 = dchannel_dcolor * dpix2;
-                            dL_dalpha *= T;
-                            last_alpha = alpha;
-                            dL_dalpha += (-T_final * inv) * bg_dot_dpixel;  // backward.cu:571-574
-                            // backward.cu:577-598.  All five geometric gradients are linear in the moments
-                            // sum(w), sum(w dx), sum(w dy), sum(w dx dx), sum(w dx dy), sum(w dy dy) with
-                            // w = dL_dG * G; only the moments are reduced here, the per-Gaussian combinations with
-                            // the conic (constant over the sum) are applied once in the preprocess backward.
-                            const float w = (b.z * dL_dalpha) * G;
-                            const float wx = w * dx, wy = w * dy;
-                            v[0] = wx;
-                            v[1] = wy;
-                            v[2] = wx * dx;
-                            v[3] = wx * dy;
-                            v[4] = wy * dy;
-                            v[5] = G * dL_dalpha;
-                        }
-                    }
-                }
-                if (__any_sync(0xffffffffu, contrib)) {
-                    reduce_scatter_step<8>(v, 16, (lane & 16) != 0);
-                    reduce_scatter_step<4>(v, 8, (lane & 8) != 0);
-                    reduce_scatter_step<2>(v, 4, (lane & 4) != 0);
-                    float r = v[0];
-                    r += __shfl_xor_sync(0xffffffffu, r, 2);
-                    r += __shfl_xor_sync(0xffffffffu, r, 1);
-#pragma unroll
-                    for (int d = 16; d > 0; d >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, d);
-                    float* dst = grad_acc + 12 * (size_t)lds32u<BOFF_ID>(sb + (uint32_t)j * 4);
-                    if ((lane & 3) == 0) atomicAdd(dst + (lane >> 2), r);
-                    else if (lane == 1) atomicAdd(dst + 8, v8);
-                }
+                for (int d = 16; d > 0; d >>= 1) v8 += __shfl_xor_sync(0xffffffffu, v8, d);
+                float* dst = grad_acc + 12 * (size_t)lds32u<BOFF_ID>(sb + (uint32_t)j * 4);
+                if (red_lane) atomicAdd(dst + red_idx, lane == 1 ? v8 : r);
             }
         }
     }
@@ -233,11 +168,8 @@ void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2*
                             cudaStream_t st) {
     if (row_end <= row_begin || grid_x <= 0) return;
     dim3 grid(grid_x, row_end - row_begin, 1);
-    static const bool pred = !(getenv("GSR_BWD_PRED") && atoi(getenv("GSR_BWD_PRED")) == 0);   // EXPERIMENT
-    if (pred) render_bwd_kernel<true><<<grid, 256, 0, st>>>(ranges, point_list, W, H, grid_x, row_begin, packed, bg, final_T, n_contrib,
-                                                            dL_dpix, grad_acc, warp_mask);
-    else render_bwd_kernel<false><<<grid, 256, 0, st>>>(ranges, point_list, W, H, grid_x, row_begin, packed, bg, final_T, n_contrib,
-                                                        dL_dpix, grad_acc, warp_mask);
+    render_bwd_kernel<<<grid, 256, 0, st>>>(ranges, point_list, W, H, grid_x, row_begin, packed, bg, final_T, n_contrib,
+                                             dL_dpix, grad_acc, warp_mask);
     count_launch(1);
 }
 
