@@ -363,7 +363,8 @@ def run_gpu(args):
                 "h2d_bytes_per_step": int(view.cam_host.numel() * 4 + (dL_host.numel() * 4 if do_bwd else 0)),
                 "d2h_bytes_per_step": 4 if do_bwd else int(3 * H * W * 4),
                 "what": ("GaussianRasterizer.forward + loss + backward through the drop-in Python API; camera and upstream "
-                         "image copied from pinned host memory every step, scalar loss read back; parameters resident") if do_bwd else
+                         "image copied from pinned host memory every step (the image on a copy stream beside the forward, as a "
+                         "training loop prefetches its next target), scalar loss read back; parameters resident") if do_bwd else
                         "camera copied from pinned host memory, frame rendered through the drop-in Python API and copied back to "
                         "pinned host memory every step; parameters resident"},
         "gpu_launches": launches,
@@ -413,7 +414,7 @@ def roofline_block(stage, P, R, N, P_vis, K, hbm_peak, peak_src, steps):
     a = stages[dom]["gbs"]
     pairs_upper = 256.0 * R
     rl = {"kernel": {"render": "render_fwd_kernel", "render_bwd": "render_bwd_kernel", "preprocess": "preprocess_fwd_kernel",
-                     "preprocess_bwd": "preprocess_bwd_kernel", "duplicate": "duplicate_kernel", "tile_ranges": "tile_ranges_kernel"}[dom],
+                     "preprocess_bwd": "preprocess_bwd_kernel_staged", "duplicate": "duplicate_coop_kernel", "tile_ranges": "tile_ranges4_kernel"}[dom],
           "bound": "hbm", "achieved": a, "peak": hbm_peak, "unit": "GB/s", "frac": round(a / hbm_peak, 4), "traffic": None,
           "peak_source": peak_src, "launch_ms": stages[dom]["ms"], "alg_bytes_per_launch": stages[dom]["alg_bytes"],
           "note": "the blending kernels are issue-slot/MUFU/shared-memory bound, not HBM bound (SURVEY.md 8(d)); the HBM "
@@ -424,6 +425,13 @@ def roofline_block(stage, P, R, N, P_vis, K, hbm_peak, peak_src, steps):
         if t.get("P") == P and t.get("num_rendered") == R and rl["kernel"] in t.get("kernels", {}):
             rl["traffic"] = t["kernels"][rl["kernel"]]
             rl["traffic_source"] = t.get("source")
+            wi = t.get("warp_instructions", {}).get(rl["kernel"])
+            if wi:      # the bound that actually holds for the blending kernels: warp-instruction issue slots (4 schedulers per SM, 1 per clock)
+                peak_gi = 148 * 4 * 1.965            # G warp-instructions/s at the 1965 MHz the run holds (see clocks)
+                ach = wi / stages[dom]["ms"] / 1e6
+                rl["issue_slots"] = {"warp_instructions_per_launch": wi, "achieved": round(ach, 1), "peak": round(peak_gi, 1),
+                                     "unit": "G warp-instr/s", "frac": round(ach / peak_gi, 4),
+                                     "source": "ncu smsp__inst_executed.sum of the committed capture / live launch time"}
     out = {"roofline": rl, "stages": stages}
     if dom in ("render", "render_bwd"):
         issue_peak = 148 * 128 * 1.965e9          # lane-instructions/s

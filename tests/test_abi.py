@@ -125,6 +125,32 @@ def test_backward_argument_checks(lib):
     assert lib.gsr_backward(None, None) == 1
 
 
+def test_backward_chunk_plan_covers_every_gaussian_once(lib):
+    """gsr_backward_chunk_plan is host arithmetic: ranges are contiguous, aligned to 256 Gaussians and cover [0, P)."""
+    b = (C.c_int * 5)()
+    for P in (0, 1, 1000, 65535, 65536, 100000, 3000000, 6000001):
+        n = lib.gsr_backward_chunk_plan(P, b)
+        assert 1 <= n <= 4
+        bounds = [b[i] for i in range(n + 1)]
+        assert bounds[0] == 0 and bounds[-1] == P
+        assert all(x <= y for x, y in zip(bounds, bounds[1:]))
+        assert all(x % 256 == 0 for x in bounds[:-1])
+        if P >= 65536:
+            assert n == 4 and 0 < bounds[1] <= P // 8       # a small head range, then the rest
+    assert lib.gsr_backward_chunk_plan(10, None) == 0
+
+
+def test_exchange_entry_points_check_their_arguments(lib):
+    lib.gsr_multimem_allreduce.argtypes = [C.c_void_p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+    assert lib.gsr_multimem_allreduce(None, 0, 16, 0, 2, None) == 1            # no multicast address
+    assert lib.gsr_multimem_allreduce(C.c_void_p(0x1000), 2, 16, 0, 2, None) == 1   # range start not 16-byte aligned
+    assert lib.gsr_multimem_allreduce(C.c_void_p(0x1000), 0, 16, 2, 2, None) == 1   # rank outside the world
+    lib.gsr_unpack_small_grads.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 7
+    assert lib.gsr_unpack_small_grads(0, 0, None, None, None, None, None, None, None) == 0    # empty range: no-op
+    assert lib.gsr_unpack_small_grads(0, 8, None, None, None, None, None, None, None) == 1
+    assert lib.gsr_unpack_small_grads(8, 0, None, None, None, None, None, None, None) == 1
+
+
 def test_launch_counter_starts_at_zero_on_cpu(lib):
     lib.gsr_launch_count.restype = C.c_ulonglong
     assert lib.gsr_launch_count() == 0
