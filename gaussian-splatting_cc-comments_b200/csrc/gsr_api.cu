@@ -337,6 +337,33 @@ int gsr_multimem_allreduce(void* multicast_base, size_t begin, size_t end, int r
     return GSR_OK;
 }
 
+size_t gsr_l1_ssim_scratch_floats(int planes, int height, int width) {
+    if (planes <= 0 || height <= 0 || width <= 0) return 0;
+    return 2 * l1_ssim_blocks(planes, height, width);
+}
+
+int gsr_l1_ssim_forward(const float* img, const float* gt, int planes, int height, int width, float lambda_dssim,
+                        float* dm_maps, float* scratch, float* out3, void* cuda_stream) {
+    if (planes <= 0 || height <= 0 || width <= 0) return fail(GSR_ERR_INVALID_ARGUMENT, "bad image sizes");
+    if (!img || !gt || !scratch || !out3) return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
+    if (l1_ssim_blocks(planes, height, width) > 0x7fffffffull || planes > 65535) return fail(GSR_ERR_INVALID_ARGUMENT, "image too large");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_l1_ssim_forward(img, gt, planes, height, width, lambda_dssim, dm_maps, scratch, out3, st);
+    GSR_STAGE("l1+ssim forward", st, 0);
+    return GSR_OK;
+}
+
+int gsr_l1_ssim_backward(const float* img, const float* gt, const float* dm_maps, int planes, int height, int width,
+                         float coef_l1, float coef_ssim, const float* grad_out, float* dL_dimg, void* cuda_stream) {
+    if (planes <= 0 || height <= 0 || width <= 0) return fail(GSR_ERR_INVALID_ARGUMENT, "bad image sizes");
+    if (!img || !gt || !dm_maps || !dL_dimg) return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
+    if (planes > 65535) return fail(GSR_ERR_INVALID_ARGUMENT, "image too large");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_l1_ssim_backward(img, gt, dm_maps, planes, height, width, coef_l1, coef_ssim, grad_out, dL_dimg, st);
+    GSR_STAGE("l1+ssim backward", st, 0);
+    return GSR_OK;
+}
+
 int gsr_backward_chunk_plan(int P, int* bounds) {
     if (!bounds || P < 0) return 0;
     int b[5];

@@ -181,6 +181,11 @@ struct PreprocessBwdArgs {
     void* const* chunk_events; int n_chunk_events;   // optional cudaEvent_t per chunk (see include/gsr.h)
     float* small_pack;         // optional (P,14): mean3D 3 | mean2D 3 | opacity 1 | scale 3 | rot 4 instead of the five tensors
 };
+size_t l1_ssim_blocks(int planes, int H, int W);
+void launch_l1_ssim_forward(const float* img, const float* gt, int planes, int H, int W, float lambda, float* dm_maps, float* partial,
+                            float* out3, cudaStream_t st);
+void launch_l1_ssim_backward(const float* img, const float* gt, const float* dm_maps, int planes, int H, int W, float coef_l1,
+                             float coef_ssim, const float* grad_out, float* dimg, cudaStream_t st);
 void launch_multimem_allreduce(float* mc_base, size_t begin, size_t end, int rank, int world, int max_blocks, cudaStream_t st);
 void launch_unpack_small(int begin, int end, const float* pack, float* dmean3D, float* dmean2D, float* dop, float* dscale,
                          float* drot, cudaStream_t st);

@@ -235,6 +235,38 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         cudaStream_t st = c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)device).stream();
         check(gsr_multimem_allreduce(reinterpret_cast<void*>(mc_ptr), (size_t)begin, (size_t)end, (int)rank, (int)world, (void*)st));
     }, "two-shot all-reduce of floats [begin,end) through an NVLS multicast address (include/gsr.h)");
+    m.def("l1_ssim_forward", [](const torch::Tensor& img, const torch::Tensor& gt, double lambda_dssim, bool need_grad) {
+        TORCH_CHECK(img.is_cuda() && gt.is_cuda(), "l1_ssim_forward: CUDA tensors only (there is no CPU path)");
+        TORCH_CHECK(img.scalar_type() == torch::kFloat32 && gt.scalar_type() == torch::kFloat32, "float32 images");
+        TORCH_CHECK(img.sizes() == gt.sizes() && img.dim() >= 3 && img.dim() <= 4 && img.device() == gt.device(), "images must have the same (C,H,W) or (B,C,H,W) shape and device");
+        const c10::cuda::CUDAGuard guard(img.device());
+        auto a = img.contiguous(), b = gt.contiguous();
+        const int H = (int)a.size(-2), W = (int)a.size(-1);
+        const int planes = (int)(a.numel() / ((int64_t)H * W));
+        auto opt = a.options();
+        torch::Tensor maps = need_grad ? torch::empty({3, (int64_t)planes, H, W}, opt) : torch::empty({0}, opt);
+        torch::Tensor scratch = torch::empty({(int64_t)gsr_l1_ssim_scratch_floats(planes, H, W)}, opt);
+        torch::Tensor out3 = torch::empty({3}, opt);
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(img.device().index()).stream();
+        check(gsr_l1_ssim_forward(a.data_ptr<float>(), b.data_ptr<float>(), planes, H, W, (float)lambda_dssim,
+                                  need_grad ? maps.data_ptr<float>() : nullptr, scratch.data_ptr<float>(), out3.data_ptr<float>(), (void*)st));
+        return std::make_tuple(out3, maps);
+    }, "fused L1 + SSIM forward: (loss, l1, ssim) and the derivative maps (include/gsr.h)");
+    m.def("l1_ssim_backward", [](const torch::Tensor& img, const torch::Tensor& gt, const torch::Tensor& maps, double coef_l1, double coef_ssim,
+                                 const torch::Tensor& grad_out) {
+        TORCH_CHECK(img.is_cuda() && gt.is_cuda() && maps.is_cuda() && grad_out.is_cuda(), "l1_ssim_backward: CUDA tensors only");
+        TORCH_CHECK(grad_out.numel() == 1 && grad_out.scalar_type() == torch::kFloat32, "grad_out: one float32 element");
+        const c10::cuda::CUDAGuard guard(img.device());
+        auto a = img.contiguous(), b = gt.contiguous(), g = grad_out.contiguous();
+        const int H = (int)a.size(-2), W = (int)a.size(-1);
+        const int planes = (int)(a.numel() / ((int64_t)H * W));
+        TORCH_CHECK(maps.is_contiguous() && maps.numel() == 3 * a.numel(), "maps: the tensor l1_ssim_forward returned for these images");
+        torch::Tensor dimg = torch::empty_like(a);
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(img.device().index()).stream();
+        check(gsr_l1_ssim_backward(a.data_ptr<float>(), b.data_ptr<float>(), maps.data_ptr<float>(), planes, H, W, (float)coef_l1, (float)coef_ssim,
+                                   g.data_ptr<float>(), dimg.data_ptr<float>(), (void*)st));
+        return dimg;
+    }, "fused L1 + SSIM backward (include/gsr.h)");
     m.def("backward_chunk_plan", [](int64_t P) {
         int b[GSR_MAX_CHUNKS + 1];
         const int n = gsr_backward_chunk_plan((int)P, b);

@@ -175,6 +175,23 @@ int gsr_unpack_small_grads(int begin, int end, const float* small_pack, float* d
  * after (all slices broadcast).  No reference counterpart (multi-view training extension). */
 int gsr_multimem_allreduce(void* multicast_base, size_t begin, size_t end, int rank, int world, void* cuda_stream);
 
+/* ---- Fused L1 + SSIM training loss (replaces utils/loss_utils.py:17-64 + train.py:126-127) ----
+ * Images are `planes` x H x W float32 (planes = channels, or batch*channels: the window is applied per plane and every
+ * mean is over all planes*H*W elements, as F.conv2d(groups = channels) + .mean() do).  Window 11, sigma 1.5, zero padding.
+ *
+ * forward : out3[0] = (1 - lambda_dssim) * mean|img - gt| + lambda_dssim * (1 - mean ssim(img, gt))   (train.py:127)
+ *           out3[1] = mean|img - gt| (l1_loss), out3[2] = mean ssim(img, gt) (ssim, size_average = True);
+ *           dm_maps (3 * planes*H*W floats, or NULL when no gradient is needed) receives the per-pixel partial
+ *           derivatives of the SSIM map the backward convolves; scratch holds gsr_l1_ssim_scratch_floats floats.
+ * backward: dL_dimg = *grad_out * (coef_l1 * sign(img - gt) + coef_ssim * d(sum of the ssim map)/d img);
+ *           for the train.py loss coef_l1 = (1 - lambda)/n, coef_ssim = -lambda/n with n = planes*H*W;
+ *           grad_out is a DEVICE scalar (NULL = 1), so no host synchronisation is needed. */
+size_t gsr_l1_ssim_scratch_floats(int planes, int height, int width);
+int gsr_l1_ssim_forward(const float* img, const float* gt, int planes, int height, int width, float lambda_dssim,
+                        float* dm_maps, float* scratch, float* out3, void* cuda_stream);
+int gsr_l1_ssim_backward(const float* img, const float* gt, const float* dm_maps, int planes, int height, int width,
+                         float coef_l1, float coef_ssim, const float* grad_out, float* dL_dimg, void* cuda_stream);
+
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      unsigned char* present /* (P) bool out */, void* cuda_stream);
 
