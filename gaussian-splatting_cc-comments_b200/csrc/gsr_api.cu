@@ -7,6 +7,7 @@
 // the API returns it as an int; it is a 4-byte async copy into pinned memory + stream sync.
 #include "../../include/gsr.h"
 #include <cstdlib>
+#include <cmath>
 #include "gsr_internal.cuh"
 #include <string>
 #include <cstdio>
@@ -361,6 +362,73 @@ int gsr_l1_ssim_backward(const float* img, const float* gt, const float* dm_maps
     cudaStream_t st = (cudaStream_t)cuda_stream;
     launch_l1_ssim_backward(img, gt, dm_maps, planes, height, width, coef_l1, coef_ssim, grad_out, dL_dimg, st);
     GSR_STAGE("l1+ssim backward", st, 0);
+    return GSR_OK;
+}
+
+// ---- fused Adam step (torch.optim.Adam as scene/gaussian_model.py:252 configures it) ----
+int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, double beta2, double eps,
+                  const unsigned char* visible, void* cuda_stream) {
+    if (n_groups < 0 || (n_groups > 0 && !groups)) return fail(GSR_ERR_INVALID_ARGUMENT, "adam: bad group list");
+    if (!(beta1 >= 0.0 && beta1 < 1.0) || !(beta2 >= 0.0 && beta2 < 1.0) || !(eps >= 0.0))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "adam: betas must be in [0,1) and eps >= 0");     // torch/optim/adam.py's own checks
+    for (int i = 0; i < n_groups; i++) {
+        const gsr_adam_group& g = groups[i];
+        if (g.n == 0) continue;
+        if (!g.param || !g.grad || !g.exp_avg || !g.exp_avg_sq) return fail(GSR_ERR_INVALID_ARGUMENT, "adam: null tensor in group " + std::to_string(i));
+        if (g.step < 1) return fail(GSR_ERR_INVALID_ARGUMENT, "adam: step must be >= 1 (the count after this update)");
+        if (!(g.lr >= 0.0)) return fail(GSR_ERR_INVALID_ARGUMENT, "adam: negative learning rate");
+        if (visible && g.row_width < 1) return fail(GSR_ERR_INVALID_ARGUMENT, "adam: row_width must be >= 1 with a visibility mask");
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    int i = 0;
+    while (i < n_groups) {
+        AdamLaunch L;
+        L.n_groups = 0;
+        L.beta2 = (float)beta2; L.w1 = (float)(1.0 - beta1); L.w2 = (float)(1.0 - beta2); L.eps = (float)eps;
+        L.visible = visible;
+        unsigned long long blocks = 0;
+        bool vec = true;
+        for (; i < n_groups && L.n_groups < ADAM_MAX_GROUPS; i++) {
+            const gsr_adam_group& g = groups[i];
+            if (g.n == 0) continue;
+            const unsigned long long nb = adam_blocks(g.n);
+            if (blocks + nb > 0x7fffffffull) {
+                if (L.n_groups == 0) return fail(GSR_ERR_INVALID_ARGUMENT, "adam: group too large for one grid");
+                break;                                           // goes into the next launch
+            }
+            AdamGroupDev& d = L.g[L.n_groups];
+            d.p = g.param; d.g = g.grad; d.m = g.exp_avg; d.v = g.exp_avg_sq; d.n = g.n;
+            // host scalars in double, as torch computes them in Python floats (torch/optim/adam.py, _multi_tensor_adam)
+            const double bc1 = 1.0 - std::pow(beta1, (double)g.step);
+            const double bc2 = 1.0 - std::pow(beta2, (double)g.step);
+            d.neg_step = (float)(-(g.lr / bc1));
+            d.bc2_sqrt = (float)std::sqrt(bc2);
+            d.row_width = (unsigned)(g.row_width > 0 ? g.row_width : 1);
+            const uintptr_t a = (uintptr_t)g.param | (uintptr_t)g.grad | (uintptr_t)g.exp_avg | (uintptr_t)g.exp_avg_sq;
+            if (a & 15) vec = false;
+            L.block_start[L.n_groups] = (unsigned)blocks;
+            blocks += nb;
+            L.n_groups++;
+        }
+        for (int k = L.n_groups; k <= ADAM_MAX_GROUPS; k++) L.block_start[k] = (unsigned)blocks;
+        for (int k = L.n_groups; k < ADAM_MAX_GROUPS; k++) L.g[k] = AdamGroupDev{nullptr, nullptr, nullptr, nullptr, 0, 0.f, 1.f, 1};
+        launch_adam(L, (unsigned)blocks, vec, st);
+        GSR_STAGE("adam step", st, 0);
+    }
+    return GSR_OK;
+}
+
+// ---- distCUDA2 of simple-knn ----
+size_t gsr_knn_scratch_bytes(int P) { return P > 0 ? KnnState::carve(nullptr, (size_t)P).bytes : 0; }
+
+int gsr_knn_mean_dist2(int P, const float* points, float* mean_dist2, char* scratch, void* cuda_stream) {
+    if (P < 0) return fail(GSR_ERR_INVALID_ARGUMENT, "knn: negative point count");
+    if (P == 0) return GSR_OK;
+    if (!points || !mean_dist2 || !scratch) return fail(GSR_ERR_INVALID_ARGUMENT, "knn: null pointer");
+    if (((uintptr_t)scratch & 255) != 0) return fail(GSR_ERR_INVALID_ARGUMENT, "knn: scratch must be 256-byte aligned");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_knn(P, points, mean_dist2, KnnState::carve(scratch, (size_t)P), st);
+    GSR_STAGE("knn", st, 0);
     return GSR_OK;
 }
 

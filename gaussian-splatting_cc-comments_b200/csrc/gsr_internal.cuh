@@ -203,6 +203,39 @@ struct MultiviewShArgs {
 };
 void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st);
 
+// ---- fused Adam step (gsr_adam.cu) -------------------------------------------------------------------
+constexpr int ADAM_MAX_GROUPS = 8;         // parameter groups per launch (the model has six)
+struct AdamGroupDev {
+    float* p; const float* g; float* m; float* v;   // param, grad, exp_avg, exp_avg_sq
+    unsigned long long n;                           // elements
+    float neg_step;                                 // -lr / (1 - beta1^t)
+    float bc2_sqrt;                                 // sqrt(1 - beta2^t)
+    unsigned row_width;                             // elements per Gaussian (visible-mask mode)
+};
+struct AdamLaunch {
+    AdamGroupDev g[ADAM_MAX_GROUPS];
+    unsigned block_start[ADAM_MAX_GROUPS + 1];      // first block of each group; [n_groups] = grid size
+    int n_groups;
+    float beta2, w1, w2, eps;                       // w1 = 1 - beta1, w2 = 1 - beta2
+    const uint8_t* visible;                         // optional (rows) mask: 0 = leave the row untouched
+};
+size_t adam_blocks(size_t n);
+void launch_adam(const AdamLaunch& L, unsigned total_blocks, bool vec, cudaStream_t st);
+
+// ---- 3-nearest-neighbour mean squared distance (gsr_knn.cu) ------------------------------------------
+struct KnnState {
+    uint32_t* keys[2];         // P each: Morton codes, ping-pong
+    uint32_t* vals[2];         // P each: point indices, ping-pong
+    uint32_t* table;           // radix sort tables, rs_table_words(P)
+    float4* sorted;            // P: (x, y, z, original index) in Morton order
+    float4* boxes;             // 2 per box: componentwise min, max
+    int* bounds;               // 6 (+2): order-preserving integer images of the scene bounds
+    size_t bytes;
+    static KnnState carve(char* base, size_t P);
+};
+size_t knn_boxes(size_t P);
+void launch_knn(int P, const float* points, float* mean_d2, const KnnState& s, cudaStream_t st);
+
 // Chunked launches for kernels that run beside a collective: a grid of tens of thousands of short blocks keeps every
 // SM full, and the collective's few large CTAs (launched a moment later on another stream) are not placed until that
 // grid drains, whatever the stream priorities.  A small head chunk followed by three equal ones gives the block

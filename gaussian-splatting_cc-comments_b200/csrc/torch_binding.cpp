@@ -267,6 +267,61 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
                                    g.data_ptr<float>(), dimg.data_ptr<float>(), (void*)st));
         return dimg;
     }, "fused L1 + SSIM backward (include/gsr.h)");
+    m.def("adam_step", [](std::vector<torch::Tensor> params, std::vector<torch::Tensor> grads, std::vector<torch::Tensor> exp_avgs,
+                          std::vector<torch::Tensor> exp_avg_sqs, std::vector<double> lrs, std::vector<int64_t> steps, double beta1, double beta2,
+                          double eps, const c10::optional<torch::Tensor>& visible) {
+        const size_t n = params.size();
+        TORCH_CHECK(grads.size() == n && exp_avgs.size() == n && exp_avg_sqs.size() == n && lrs.size() == n && steps.size() == n,
+                    "adam_step: one grad, exp_avg, exp_avg_sq, lr and step per parameter");
+        if (n == 0) return;
+        const auto dev = params[0].device();
+        TORCH_CHECK(dev.is_cuda(), "adam_step: CUDA tensors only (there is no CPU path)");
+        std::vector<gsr_adam_group> groups(n);
+        int64_t rows = -1;
+        if (visible.has_value()) {
+            TORCH_CHECK(visible->is_cuda() && visible->device() == dev && visible->is_contiguous() && visible->dim() == 1 &&
+                        (visible->scalar_type() == torch::kBool || visible->scalar_type() == torch::kUInt8),
+                        "adam_step: visible must be a contiguous (P,) bool / uint8 tensor on the parameters' device");
+            rows = visible->numel();
+        }
+        for (size_t i = 0; i < n; i++) {
+            for (const torch::Tensor* t : {&params[i], &grads[i], &exp_avgs[i], &exp_avg_sqs[i]})
+                TORCH_CHECK(t->is_cuda() && t->device() == dev && t->scalar_type() == torch::kFloat32 && t->is_contiguous() &&
+                            t->numel() == params[i].numel(), "adam_step: contiguous float32 tensors of the parameter's size on one CUDA device");
+            groups[i].param = params[i].data_ptr<float>();
+            groups[i].grad = grads[i].data_ptr<float>();
+            groups[i].exp_avg = exp_avgs[i].data_ptr<float>();
+            groups[i].exp_avg_sq = exp_avg_sqs[i].data_ptr<float>();
+            groups[i].n = (size_t)params[i].numel();
+            groups[i].lr = lrs[i];
+            groups[i].step = (long long)steps[i];
+            groups[i].row_width = 1;
+            if (rows >= 0) {
+                TORCH_CHECK(params[i].dim() >= 1 && params[i].size(0) == rows, "adam_step: with `visible`, every parameter's first dimension is P");
+                groups[i].row_width = rows > 0 ? (int)(params[i].numel() / rows) : 1;
+            }
+        }
+        const c10::cuda::CUDAGuard guard(dev);
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(gsr_adam_step(groups.data(), (int)n, beta1, beta2, eps,
+                            visible.has_value() ? reinterpret_cast<const unsigned char*>(visible->data_ptr()) : nullptr, (void*)st));
+    }, "one-launch Adam step over all parameter groups, in place (include/gsr.h: gsr_adam_step)",
+          py::arg("params"), py::arg("grads"), py::arg("exp_avgs"), py::arg("exp_avg_sqs"), py::arg("lrs"), py::arg("steps"), py::arg("beta1"),
+          py::arg("beta2"), py::arg("eps"), py::arg("visible") = py::none());
+    m.def("dist_cuda2", [](const torch::Tensor& points) {
+        TORCH_CHECK(points.is_cuda(), "distCUDA2: CUDA tensor only (there is no CPU path)");
+        TORCH_CHECK(points.scalar_type() == torch::kFloat32 && points.dim() == 2 && points.size(1) == 3, "distCUDA2: points must be (P,3) float32");
+        const c10::cuda::CUDAGuard guard(points.device());
+        auto pts = points.contiguous();
+        const int64_t P = pts.size(0);
+        TORCH_CHECK(P <= 0x7fffffffll, "distCUDA2: too many points");
+        torch::Tensor means = torch::full({P}, 0.0, pts.options());                       // spatial.cu:21
+        if (P == 0) return means;
+        torch::Tensor scratch = torch::empty({(int64_t)gsr_knn_scratch_bytes((int)P)}, pts.options().dtype(torch::kUInt8));
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(points.device().index()).stream();
+        check(gsr_knn_mean_dist2((int)P, pts.data_ptr<float>(), means.data_ptr<float>(), reinterpret_cast<char*>(scratch.data_ptr()), (void*)st));
+        return means;
+    }, "mean squared distance to the 3 nearest neighbours (include/gsr.h: gsr_knn_mean_dist2; simple-knn's distCUDA2)");
     m.def("backward_chunk_plan", [](int64_t P) {
         int b[GSR_MAX_CHUNKS + 1];
         const int n = gsr_backward_chunk_plan((int)P, b);

@@ -192,6 +192,39 @@ int gsr_l1_ssim_forward(const float* img, const float* gt, int planes, int heigh
 int gsr_l1_ssim_backward(const float* img, const float* gt, const float* dm_maps, int planes, int height, int width,
                          float coef_l1, float coef_ssim, const float* grad_out, float* dL_dimg, void* cuda_stream);
 
+/* ---- Fused Adam step over all parameter groups ----
+ * Replaces `self.optimizer.step()` (train.py:173-175) for the optimizer scene/gaussian_model.py:243-252 builds:
+ * torch.optim.Adam(l, lr=0.0, eps=1e-15), six groups, no weight decay, no amsgrad.  One kernel launch updates every group
+ * in place (28 bytes of traffic per element) with torch's arithmetic in torch's order:
+ *     exp_avg    <- exp_avg + (1 - beta1) * (grad - exp_avg)
+ *     exp_avg_sq <- exp_avg_sq * beta2 + (1 - beta2) * grad * grad
+ *     param      <- param - lr / (1 - beta1^step) * exp_avg / (sqrt(exp_avg_sq) / sqrt(1 - beta2^step) + eps)
+ * `step` is the group's step count AFTER this update (torch increments state['step'] before using it), so >= 1.
+ * `visible` (optional, NULL = off; NOT the reference's semantics): one byte per Gaussian; rows with 0 are left
+ * untouched -- parameters and both moments -- where row = element / row_width.  Groups with n == 0 are skipped. */
+typedef struct gsr_adam_group {
+    float* param;            /* (n) in/out */
+    const float* grad;       /* (n) */
+    float* exp_avg;          /* (n) in/out, first moment  (state['exp_avg'])    */
+    float* exp_avg_sq;       /* (n) in/out, second moment (state['exp_avg_sq']) */
+    size_t n;                /* elements */
+    double lr;               /* the group's learning rate for this step (param_group['lr']) */
+    long long step;          /* >= 1 */
+    int row_width;           /* elements per Gaussian: 3, 3, 45, 1, 3, 4 for the six groups; used only with `visible` */
+} gsr_adam_group;
+int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, double beta2, double eps,
+                  const unsigned char* visible, void* cuda_stream);
+
+/* ---- Mean squared distance to the 3 nearest neighbours ----
+ * Replaces distCUDA2 of the reference's simple-knn extension (submodules/simple-knn/spatial.cu:15-26, SimpleKNN::knn,
+ * simple_knn.cu:185-221), used by GaussianModel.create_from_pcd to initialise the scales (scene/gaussian_model.py:207).
+ * mean_dist2[i] = (d0 + d1 + d2) / 3 with d0 <= d1 <= d2 the three smallest squared distances from point i to the
+ * other points (other = different index: coincident points count with distance 0); fewer than 4 points give +inf,
+ * as the reference's FLT_MAX initialisation does.  points is (P,3) float32, scratch holds gsr_knn_scratch_bytes(P)
+ * bytes (256-byte aligned) and is free again when the call's work on the stream is done.  No host synchronisation. */
+size_t gsr_knn_scratch_bytes(int P);
+int gsr_knn_mean_dist2(int P, const float* points, float* mean_dist2, char* scratch, void* cuda_stream);
+
 int gsr_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                      unsigned char* present /* (P) bool out */, void* cuda_stream);
 

@@ -13,6 +13,10 @@ No -use_fast_math, matching the reference's setup.py:29.
 
 Result:  oracle/_ref/diff_gaussian_rasterization/{__init__.py,_C.so}
          (the same layout `pip install --target` would give).
+
+build_knn() does the same for the reference's simple-knn extension (submodules/simple-knn: spatial.cu, simple_knn.cu,
+ext.cpp; stock flags, `-include cfloat` for FLT_MAX under gcc 13) -> oracle/_ref/simple_knn/_C.so, the checker of
+gsr_knn_mean_dist2 on the GPU box.
 """
 import os, shutil, sys, glob
 
@@ -51,6 +55,35 @@ def build(verbose=False):
     return True
 
 
+REF_KNN = "/root/reference/submodules/simple-knn"
+PKG_KNN = os.path.join(OUT, "simple_knn")
+
+
+def build_knn(verbose=False):
+    if not os.path.isdir(REF_KNN):
+        return False  # GPU box: only the prebuilt files exist
+    os.makedirs(PKG_KNN, exist_ok=True)
+    so = os.path.join(PKG_KNN, "_C.so")
+    srcs = [os.path.join(REF_KNN, p) for p in ("spatial.cu", "simple_knn.cu", "ext.cpp")]
+    if os.path.exists(so) and os.path.getmtime(so) >= max(os.path.getmtime(s) for s in srcs):
+        return True
+    os.environ["TORCH_CUDA_ARCH_LIST"] = "10.0"
+    os.environ.setdefault("MAX_JOBS", "8")
+    from torch.utils.cpp_extension import load
+    bdir = os.path.join(OUT, "build_knn")
+    os.makedirs(bdir, exist_ok=True)
+    load(name="_C", sources=srcs, extra_cuda_cflags=["-include", "cfloat", "-include", "cstdint"],
+         build_directory=bdir, verbose=verbose, is_python_module=False)
+    built = glob.glob(os.path.join(bdir, "_C*.so"))
+    assert built, "reference simple-knn build produced no .so"
+    shutil.copy2(built[0], so)
+    with open(os.path.join(PKG_KNN, "__init__.py"), "w"):
+        pass   # the reference's package directory holds only the compiled module (submodules/simple-knn/simple_knn/.gitkeep)
+    return True
+
+
 if __name__ == "__main__":
     ok = build(verbose="-v" in sys.argv)
     print("reference build:", "ok" if ok else "skipped (no /root/reference)")
+    ok = build_knn(verbose="-v" in sys.argv)
+    print("reference simple-knn build:", "ok" if ok else "skipped (no /root/reference)")

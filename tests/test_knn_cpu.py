@@ -1,0 +1,46 @@
+"""Oracle of simple-knn's distCUDA2 (oracle/gs_next_oracle.c: gno_knn_mean_d2) against an independent exact search.
+
+The reference function is CUDA only and ships no vectors, so the oracle is not pinned to the reference binary this round
+("parity unpinned", see the oracle's header); its definition -- mean of the three smallest squared distances to other
+points -- is checked against scipy's cKDTree in float64.  CPU only."""
+import numpy as np
+import pytest
+from scipy.spatial import cKDTree
+
+from oracle import gs_next_oracle as O
+
+
+def _exact(pts):
+    p = np.asarray(pts, np.float32).astype(np.float64)
+    d, _ = cKDTree(p).query(p, k=4)
+    return (d[:, 1:] ** 2).mean(axis=1)            # column 0 is the point itself (or a coincident twin at distance 0)
+
+
+@pytest.mark.parametrize("P,seed", [(4, 0), (5, 1), (1000, 2), (5000, 3), (40000, 4)])
+def test_oracle_is_the_exact_3nn_mean(P, seed):
+    rng = np.random.default_rng(seed)
+    pts = rng.normal(size=(P, 3)).astype(np.float32) * rng.choice([0.01, 1.0, 30.0])
+    if P >= 1000:
+        pts[:50] = pts[50:100]                      # coincident pairs count with distance 0 (exclusion is by index)
+    got = O.knn_mean_dist2(pts)
+    want = _exact(pts)
+    assert np.abs(got - want).max() <= 2e-6 * want.max()
+    assert np.all(np.abs(got - want) <= 1e-5 * np.maximum(want, 1e-12) + 1e-12)
+
+
+def test_fewer_than_four_points_keep_the_flt_max_placeholders():
+    """best[] starts at FLT_MAX (simple_knn.cu:159); with fewer than three neighbours the placeholders stay in the mean."""
+    fmax = np.finfo(np.float32).max
+    assert np.isinf(O.knn_mean_dist2(np.zeros((1, 3), np.float32))).all()
+    assert np.isinf(O.knn_mean_dist2(np.array([[0, 0, 0], [1, 0, 0]], np.float32))).all()
+    three = O.knn_mean_dist2(np.array([[0, 0, 0], [1, 0, 0], [0, 2, 0]], np.float32))
+    assert np.all(np.isfinite(three)) and np.all(three > fmax / 3.5)
+    assert O.knn_mean_dist2(np.zeros((0, 3), np.float32)).shape == (0,)
+
+
+def test_scale_initialisation_expression_of_the_reference():
+    """scene/gaussian_model.py:207-208: scales = log(sqrt(clamp_min(dist2, 1e-7))) repeated over 3 axes -- finite for
+    coincident points because of the clamp."""
+    pts = np.zeros((10, 3), np.float32)
+    d2 = np.maximum(O.knn_mean_dist2(pts), 1e-7)
+    assert np.allclose(np.log(np.sqrt(d2)), np.log(np.sqrt(1e-7)))

@@ -1,0 +1,195 @@
+"""GPU parity of the SURVEY 8(f) rows built after the rasterizer: the fused Adam step (row 2) and distCUDA2 (row 4).
+
+Named to sort last and marked `first_gpu_run`: these kernels were written after round 1's GPU minutes were spent, so
+their first execution on a B200 is the driver's round-end run.  They pass bit for bit under the host emulation
+(tests/test_kernels_emulated.py); here they go through the public Python API -> torch binding -> C ABI.
+
+Bars.  Adam: parameters and moments within 1e-6 relative to each tensor's largest magnitude of torch.optim.Adam's (the
+reference's optimizer; the CPU fixture and torch's own CUDA kernels) and bit-exact against the oracle.  distCUDA2:
+bit-exact against the oracle and, when oracle/_ref holds it, against the reference's own simple-knn build."""
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+from helpers import ROOT
+
+pytestmark = [pytest.mark.gpu, pytest.mark.first_gpu_run]
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_adam_cpu.npz")
+NAMES = ["xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation"]
+SHAPES = {"xyz": (3,), "f_dc": (1, 3), "f_rest": (15, 3), "opacity": (1,), "scaling": (3,), "rotation": (4,)}
+
+
+def _close(a, b, tol=1e-6):
+    a = a.detach().cpu().numpy() if hasattr(a, "detach") else np.asarray(a)
+    b = b.detach().cpu().numpy() if hasattr(b, "detach") else np.asarray(b)
+    assert a.shape == b.shape
+    return float(np.abs(a - b).max()) <= tol * max(float(np.abs(b).max()), 1e-30)
+
+
+def _ref_knn():
+    so = os.path.join(ROOT, "oracle", "_ref", "simple_knn", "_C.so")
+    if not os.path.exists(so):
+        return None
+    spec = importlib.util.spec_from_file_location("_C", so)
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
+# ------------------------------------------------------------------------------------------------ Adam
+def test_fused_adam_follows_the_golden_trajectory():
+    import gsr_optim
+    z = np.load(GOLD)
+    steps = int(z["steps"])
+    params = {n: torch.nn.Parameter(torch.tensor(z["init_" + n], device="cuda")) for n in NAMES}
+    groups = [{"params": [params[n]], "lr": float(z["lr_" + n]), "name": n} for n in NAMES]
+    opt = gsr_optim.FusedAdam(groups, lr=0.0, eps=1e-15)
+    launches0 = _launches()
+    for it in range(steps):
+        if it == 3:      # cat_tensors_to_optimizer (scene/gaussian_model.py:447-471), as the fixture's generator did
+            for group in opt.param_groups:
+                ext = torch.tensor(z["ext_" + group["name"]], device="cuda")
+                st = opt.state.get(group["params"][0], None)
+                st["exp_avg"] = torch.cat((st["exp_avg"], torch.zeros_like(ext)), dim=0)
+                st["exp_avg_sq"] = torch.cat((st["exp_avg_sq"], torch.zeros_like(ext)), dim=0)
+                del opt.state[group["params"][0]]
+                group["params"][0] = torch.nn.Parameter(torch.cat((group["params"][0].detach(), ext), dim=0).requires_grad_(True))
+                opt.state[group["params"][0]] = st
+        for group in opt.param_groups:
+            if group["name"] == "xyz":
+                group["lr"] = float(z["xyz_lr_step%d" % it])
+            group["params"][0].grad = torch.tensor(z["grad_%s_step%d" % (group["name"], it)], device="cuda")
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        for group in opt.param_groups:
+            n = group["name"]
+            st = opt.state[group["params"][0]]
+            assert float(st["step"]) == it + 1
+            assert _close(group["params"][0], z["param_%s_step%d" % (n, it)]), (n, it, "param")
+            assert _close(st["exp_avg"], z["exp_avg_%s_step%d" % (n, it)]), (n, it, "exp_avg")
+            assert _close(st["exp_avg_sq"], z["exp_avg_sq_%s_step%d" % (n, it)]), (n, it, "exp_avg_sq")
+    assert _launches() - launches0 == steps          # ONE kernel per optimizer step, all six groups
+
+
+def _launches():
+    import ctypes as C
+    lib = C.CDLL(os.path.join(ROOT, "gaussian-splatting_cc-comments_b200", "libgsr_b200.so"))
+    lib.gsr_launch_count.restype = C.c_ulonglong
+    return int(lib.gsr_launch_count())
+
+
+@pytest.mark.parametrize("P", [1, 1000, 200_003])
+def test_fused_adam_equals_torch_adam_on_the_gpu_and_the_oracle(P):
+    import gsr_optim
+    from oracle import gs_next_oracle as O
+    g = torch.Generator(device="cpu").manual_seed(P)
+    init = {n: torch.randn(P, *SHAPES[n], generator=g) for n in NAMES}
+    lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, f_rest=1.25e-4, opacity=0.05, scaling=0.005, rotation=0.001)
+
+    def make(cls):
+        ps = {n: torch.nn.Parameter(init[n].clone().cuda()) for n in NAMES}
+        return ps, cls([{"params": [ps[n]], "lr": lrs[n], "name": n} for n in NAMES], lr=0.0, eps=1e-15)
+    mine_p, mine = make(gsr_optim.FusedAdam)
+    ref_p, ref = make(torch.optim.Adam)
+    cpu = {n: [init[n].numpy().copy().reshape(-1), np.zeros(init[n].numel(), np.float32), np.zeros(init[n].numel(), np.float32)] for n in NAMES}
+    for it in range(4):
+        for n in NAMES:
+            gr = torch.randn(P, *SHAPES[n], generator=g) * (10.0 ** torch.randint(-6, 1, (P,) + (1,) * len(SHAPES[n]), generator=g).float())
+            gr[torch.rand(P, generator=g) < 0.3] = 0.0
+            mine_p[n].grad = gr.cuda()
+            ref_p[n].grad = gr.cuda()
+            O.adam_step(cpu[n][0], gr.numpy().reshape(-1), cpu[n][1], cpu[n][2], lrs[n], it + 1)
+        mine.step()
+        ref.step()
+        for n in NAMES:
+            assert _close(mine_p[n], ref_p[n]), (n, it)
+            assert _close(mine.state[mine_p[n]]["exp_avg"], ref.state[ref_p[n]]["exp_avg"]), (n, it)
+            assert _close(mine.state[mine_p[n]]["exp_avg_sq"], ref.state[ref_p[n]]["exp_avg_sq"]), (n, it)
+            assert np.array_equal(mine_p[n].detach().cpu().numpy().reshape(-1), cpu[n][0]), (n, it, "oracle")
+            assert np.array_equal(mine.state[mine_p[n]]["exp_avg_sq"].cpu().numpy().reshape(-1), cpu[n][2]), (n, it, "oracle")
+
+
+def test_fused_adam_unaligned_views_and_visibility_mask():
+    from diff_gaussian_rasterization import _C
+    from oracle import gs_next_oracle as O
+    g = torch.Generator().manual_seed(5)
+    P, w = 1203, 3
+    raw = [torch.randn(P * w + 1, generator=g).cuda() for _ in range(2)] + [torch.rand(P * w + 1, generator=g).cuda() * 0.01 for _ in range(2)]
+    p, gr, m, v = [t[1:].view(P, w) for t in raw]                    # 4-byte aligned only: the element-wise kernel
+    v.copy_(torch.rand(P, w, generator=g) * 0.01)
+    host = [t.cpu().numpy().copy().reshape(-1) for t in (p, gr, m, v)]
+    _C.adam_step([p], [gr], [m], [v], [0.01], [3], 0.9, 0.999, 1e-15)
+    O.adam_step(host[0], host[1], host[2], host[3], 0.01, 3)
+    assert np.array_equal(p.cpu().numpy().reshape(-1), host[0]) and np.array_equal(m.cpu().numpy().reshape(-1), host[2])
+    # visibility mask: rows with 0 keep parameters and both moments
+    vis = torch.rand(P, generator=g) < 0.5
+    before = [t.clone() for t in (p, m, v)]
+    _C.adam_step([p], [gr], [m], [v], [0.01], [4], 0.9, 0.999, 1e-15, vis.cuda())
+    O.adam_step(host[0], host[1], host[2], host[3], 0.01, 4)
+    rows = vis.numpy().repeat(w)
+    for t, b, h in zip((p, m, v), before, (host[0], host[2], host[3])):
+        assert np.array_equal(t.cpu().numpy().reshape(-1), np.where(rows, h, b.cpu().numpy().reshape(-1)))
+    with pytest.raises(RuntimeError):
+        _C.adam_step([p], [gr], [m], [v], [0.01], [0], 0.9, 0.999, 1e-15)          # step must be >= 1
+
+
+# ------------------------------------------------------------------------------------------------ distCUDA2
+def _points(P, seed):
+    rng = np.random.default_rng(seed)
+    kind = seed % 3
+    if kind == 0:
+        p = rng.normal(size=(P, 3))
+    elif kind == 1:
+        p = np.concatenate([rng.normal(size=(P // 2, 3)) * 0.02 - 4.0, rng.uniform(-30, 30, size=(P - P // 2, 3))])
+    else:
+        p = rng.uniform(size=(P, 3)) * np.array([100.0, 1.0, 0.01])
+    p = p.astype(np.float32)
+    if P >= 100:
+        p[:20] = p[20:40]
+    return p
+
+
+@pytest.mark.parametrize("P,seed", [(1, 0), (2, 1), (3, 2), (4, 3), (255, 4), (256, 5), (257, 6), (5000, 7), (100_000, 8), (300_001, 9)])
+def test_dist_cuda2_is_bit_exact_against_the_oracle_and_the_reference_build(P, seed):
+    from simple_knn._C import distCUDA2
+    from oracle import gs_next_oracle as O
+    pts = _points(P, seed)
+    dev = torch.tensor(pts, device="cuda")
+    got = distCUDA2(dev)
+    assert got.shape == (P,) and got.dtype == torch.float32 and got.is_cuda
+    want = O.knn_mean_dist2(pts)
+    assert np.array_equal(got.cpu().numpy(), want)
+    ref = _ref_knn()
+    if ref is not None:
+        assert np.array_equal(ref.distCUDA2(dev).cpu().numpy(), got.cpu().numpy())
+
+
+def test_dist_cuda2_empty_non_contiguous_and_wrong_inputs():
+    from simple_knn._C import distCUDA2
+    assert distCUDA2(torch.zeros(0, 3, device="cuda")).shape == (0,)
+    base = torch.randn(500, 6, device="cuda")
+    view = base[:, ::2]
+    assert torch.equal(distCUDA2(view), distCUDA2(view.contiguous()))
+    with pytest.raises(RuntimeError):
+        distCUDA2(torch.zeros(5, 3))
+    with pytest.raises(RuntimeError):
+        distCUDA2(torch.zeros(5, 2, device="cuda"))
+    # the expression of scene/gaussian_model.py:207-208 stays finite for coincident points
+    d2 = torch.clamp_min(distCUDA2(torch.zeros(300, 3, device="cuda")), 0.0000001)
+    assert torch.isfinite(torch.log(torch.sqrt(d2))).all()
+
+
+def test_dist_cuda2_one_million_points_against_a_sampled_exact_search():
+    from scipy.spatial import cKDTree
+    from simple_knn._C import distCUDA2
+    pts = _points(1_000_000, 10)
+    got = distCUDA2(torch.tensor(pts, device="cuda")).cpu().numpy()
+    idx = np.random.default_rng(0).choice(len(pts), 20000, replace=False)
+    p64 = pts.astype(np.float64)
+    d, _ = cKDTree(p64).query(p64[idx], k=4)
+    want = (d[:, 1:] ** 2).mean(axis=1)
+    assert np.all(np.abs(got[idx] - want) <= 1e-5 * np.maximum(want, 1e-12) + 1e-12)
