@@ -412,6 +412,7 @@ int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, doub
         }
         for (int k = L.n_groups; k <= ADAM_MAX_GROUPS; k++) L.block_start[k] = (unsigned)blocks;
         for (int k = L.n_groups; k < ADAM_MAX_GROUPS; k++) L.g[k] = AdamGroupDev{nullptr, nullptr, nullptr, nullptr, 0, 0.f, 1.f, 1};
+        if (blocks == 0) continue;                               // only empty groups in this batch
         launch_adam(L, (unsigned)blocks, vec, st);
         GSR_STAGE("adam step", st, 0);
     }

@@ -243,7 +243,7 @@ KnnState KnnState::carve(char* base, size_t P) {
     return s;
 }
 
-#ifndef GSR_EMU   // tests/cuda_emu compiles the kernels above for the host and brings its own launcher
+#ifndef GSR_EMU   // defined only by the host-compiled kernel check in tests/, which brings its own launcher
 void launch_knn(int P, const float* points, float* mean_d2, const KnnState& s, cudaStream_t st) {
     if (P <= 0) return;
     cudaMemsetAsync(s.bounds, 0, 8 * sizeof(int), st);

@@ -41,6 +41,7 @@ def _built():
     ext = os.path.join(G.PKG, "diff_gaussian_rasterization", "_C.so")
     if not (os.path.exists(lib) and os.path.exists(ext)):
         G.build()
-    from oracle import gs_oracle
+    from oracle import gs_oracle, gs_next_oracle
     gs_oracle.build()
+    gs_next_oracle.build()
     yield

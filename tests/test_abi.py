@@ -151,6 +151,48 @@ def test_exchange_entry_points_check_their_arguments(lib):
     assert lib.gsr_unpack_small_grads(8, 0, None, None, None, None, None, None, None) == 1
 
 
+class AdamGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("n", C.c_size_t),
+                ("lr", C.c_double), ("step", C.c_longlong), ("row_width", C.c_int)]
+
+
+def test_adam_and_knn_entry_points_check_their_arguments(lib):
+    lib.gsr_adam_step.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_void_p, C.c_void_p]
+    lib.gsr_last_error.restype = C.c_char_p
+    assert lib.gsr_adam_step(None, 0, 0.9, 0.999, 1e-15, None, None) == 0                 # no groups: no-op
+    assert lib.gsr_adam_step(None, 2, 0.9, 0.999, 1e-15, None, None) == 1
+    g = (AdamGroup * 1)()
+    g[0].n = 0
+    assert lib.gsr_adam_step(g, 1, 0.9, 0.999, 1e-15, None, None) == 0                    # empty group: skipped, no launch
+    assert lib.gsr_adam_step(g, 1, 1.0, 0.999, 1e-15, None, None) == 1                    # beta1 outside [0,1), as torch rejects it
+    assert lib.gsr_adam_step(g, 1, 0.9, 0.999, -1.0, None, None) == 1
+    g[0].n = 16
+    assert lib.gsr_adam_step(g, 1, 0.9, 0.999, 1e-15, None, None) == 1                    # null tensors
+    assert b"null tensor" in lib.gsr_last_error()
+    g[0].param = g[0].grad = g[0].exp_avg = g[0].exp_avg_sq = 0x1000
+    g[0].step = 0
+    assert lib.gsr_adam_step(g, 1, 0.9, 0.999, 1e-15, None, None) == 1                    # step counts from 1
+    assert b"step" in lib.gsr_last_error()
+    g[0].step = 1
+    g[0].lr = -1.0
+    assert lib.gsr_adam_step(g, 1, 0.9, 0.999, 1e-15, None, None) == 1
+    g[0].lr = 0.1
+    g[0].row_width = 0
+    assert lib.gsr_adam_step(g, 1, 0.9, 0.999, 1e-15, C.c_void_p(0x2000), None) == 1     # mask needs a row width
+
+    lib.gsr_knn_scratch_bytes.restype = C.c_size_t
+    lib.gsr_knn_scratch_bytes.argtypes = [C.c_int]
+    assert lib.gsr_knn_scratch_bytes(0) == 0
+    per = lib.gsr_knn_scratch_bytes(10**6) / 1e6
+    assert 32 <= per <= 48                         # 2 x (code + index) ping-pong + 16 B sorted record + tables and boxes
+    assert lib.gsr_knn_scratch_bytes(10**6) % 256 == 0
+    lib.gsr_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    assert lib.gsr_knn_mean_dist2(0, None, None, None, None) == 0                         # nothing to do
+    assert lib.gsr_knn_mean_dist2(-1, None, None, None, None) == 1
+    assert lib.gsr_knn_mean_dist2(5, None, None, None, None) == 1
+    assert lib.gsr_knn_mean_dist2(5, C.c_void_p(0x1000), C.c_void_p(0x2000), C.c_void_p(0x3010), None) == 1   # scratch alignment
+
+
 def test_launch_counter_starts_at_zero_on_cpu(lib):
     lib.gsr_launch_count.restype = C.c_ulonglong
     assert lib.gsr_launch_count() == 0
@@ -160,7 +202,7 @@ def test_library_has_no_cpu_fallback_symbols():
     """The product library must not link the oracle."""
     import subprocess
     out = subprocess.run(["nm", "-D", LIB], capture_output=True, text=True).stdout
-    assert "gso_" not in out
+    assert "gso_" not in out and "gno_" not in out and "emu_" not in out
     ext = os.path.join(ROOT, "gaussian-splatting_cc-comments_b200", "diff_gaussian_rasterization", "_C.so")
     out = subprocess.run(["nm", "-D", ext], capture_output=True, text=True).stdout
-    assert "gso_" not in out
+    assert "gso_" not in out and "gno_" not in out
