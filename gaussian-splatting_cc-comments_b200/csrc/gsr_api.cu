@@ -141,11 +141,14 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     if (a->P == 0) return GSR_OK;     // rasterize_points.cu:94
     if (!a->means3D || !a->opacities || !a->viewmatrix || !a->projmatrix || !a->cam_pos || !a->background || !a->out_color)
         return fail(GSR_ERR_INVALID_ARGUMENT, "missing required pointer");
-    if (!a->colors_precomp && (!a->shs || a->M <= 0))
+    const bool split_sh = a->features_dc != nullptr;
+    if (split_sh && (a->shs || a->colors_precomp || a->M <= 0 || (a->M > 1 && !a->features_rest)))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "split SH storage: features_dc (P,1,3) + features_rest (P,M-1,3), no shs / colors_precomp");
+    if (!a->colors_precomp && !split_sh && (!a->shs || a->M <= 0))
         return fail(GSR_ERR_INVALID_ARGUMENT, "provide SHs or precomputed colours");
     if (!a->cov3D_precomp && (!a->scales || !a->rotations))
         return fail(GSR_ERR_INVALID_ARGUMENT, "provide scales+rotations or a precomputed 3D covariance");
-    if (a->shs && (a->D < 0 || a->D > 3 || (a->D + 1) * (a->D + 1) > a->M))
+    if ((a->shs || split_sh) && (a->D < 0 || a->D > 3 || (a->D + 1) * (a->D + 1) > a->M))
         return fail(GSR_ERR_INVALID_ARGUMENT, "SH degree does not fit M coefficients");
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const int P = a->P, W = a->width, H = a->height;
@@ -177,6 +180,7 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     pa.radii = radii; pa.packed = geom.packed; pa.tiles_touched = geom.tiles_touched; pa.clamped = geom.clamped;
     pa.depth_keys = geom.keys[0]; pa.ids = geom.vals[0];
     pa.total = geom.total;
+    pa.raw_act = a->raw_activations ? 1 : 0; pa.f_dc = a->features_dc; pa.f_rest = a->features_rest;
     GSR_CUDA(cudaMemsetAsync(geom.total, 0, sizeof(uint32_t), st));
     { StageTimer t(ST_PREPROCESS, st); launch_preprocess(pa, st); }
     GSR_STAGE("preprocess", st, a->debug);
@@ -264,9 +268,17 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     if (!a->means3D || !a->radii || !a->geom_buffer || !a->binning_buffer || !a->image_buffer || !a->dL_dpix ||
         !a->viewmatrix || !a->projmatrix || !a->cam_pos || !a->background || !a->grad_scratch)
         return fail(GSR_ERR_INVALID_ARGUMENT, "missing required pointer");
+    const bool split_sh = a->features_dc != nullptr;
     if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dcolor || !a->dL_dmean3D || !a->dL_dcov3D || !a->dL_dscale || !a->dL_drot ||
-        (a->M > 0 && !a->dL_dsh))
+        (a->M > 0 && !split_sh && !a->dL_dsh))
         return fail(GSR_ERR_INVALID_ARGUMENT, "missing output pointer");
+    if (split_sh) {
+        if (a->shs || a->dL_dsh || a->colors_precomp || a->M <= 0 || a->M > 16 || !a->dL_dfeatures_dc || (a->M > 1 && (!a->features_rest || !a->dL_dfeatures_rest)))
+            return fail(GSR_ERR_INVALID_ARGUMENT, "split SH storage: features_dc/_rest with dL_dfeatures_dc/_rest, M <= 16, no shs / dL_dsh / colors_precomp");
+        if (a->rotations && ((uintptr_t)a->rotations & 15)) return fail(GSR_ERR_INVALID_ARGUMENT, "split SH storage: rotations must be 16-byte aligned");
+    }
+    if ((split_sh || a->raw_activations) && (a->dL_drgb || a->small_pack))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "the raw-parameter path is not combined with the multi-view exchange options");
     cudaStream_t st = (cudaStream_t)cuda_stream;
     const int P = a->P, W = a->width, H = a->height;
     const int grid_x = (W + GSR_TILE_X - 1) / GSR_TILE_X, grid_y = (H + GSR_TILE_Y - 1) / GSR_TILE_Y;
@@ -309,6 +321,8 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
     pb.dL_drgb = early_drgb ? nullptr : a->dL_drgb; pb.skip_dsh = (a->dL_drgb != nullptr && a->skip_dL_dsh) ? 1 : 0;
     pb.begin = 0; pb.chunked = a->dL_drgb != nullptr;
     pb.small_pack = a->small_pack;
+    pb.raw_act = a->raw_activations ? 1 : 0; pb.f_dc = a->features_dc; pb.f_rest = a->features_rest;
+    pb.dL_df_dc = a->dL_dfeatures_dc; pb.dL_df_rest = a->dL_dfeatures_rest;
     pb.chunk_events = a->chunk_done_events;
     pb.n_chunk_events = a->chunk_done_events ? (a->n_chunk_events < GSR_MAX_CHUNKS ? a->n_chunk_events : GSR_MAX_CHUNKS) : 0;
     { StageTimer t(ST_PREPROCESS_BWD, st); launch_preprocess_backward(pb, st); }

@@ -135,6 +135,10 @@ struct PreprocessArgs {
     int* radii;                // may alias an internal array
     float4* packed; uint32_t* tiles_touched; uint8_t* clamped; uint32_t* depth_keys; uint32_t* ids;
     uint32_t* total;           // zeroed by the caller; receives the sum of tiles_touched (num_rendered)
+    // raw-parameter path (gsr_fused_params.cuh); appended so that the reference-shaped kernel's parameter offsets stay put
+    int raw_act;               // opacities / scales / rotations are logits / log-scales / unnormalised quaternions
+    const float* f_dc;         // (P,1,3) and
+    const float* f_rest;       // (P,M-1,3): SH coefficients in split storage (then shs == nullptr)
 };
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st);
 void launch_mark_visible(int P, const float* means, const float* view, unsigned char* present, cudaStream_t st);
@@ -180,6 +184,10 @@ struct PreprocessBwdArgs {
     int chunked;               // a collective runs beside this kernel: launch it in chunks (chunk_plan)
     void* const* chunk_events; int n_chunk_events;   // optional cudaEvent_t per chunk (see include/gsr.h)
     float* small_pack;         // optional (P,14): mean3D 3 | mean2D 3 | opacity 1 | scale 3 | rot 4 instead of the five tensors
+    // raw-parameter path (gsr_fused_params.cuh), appended
+    int raw_act;               // scales / rotations hold raw parameters; dL_dscale / dL_drot / dL_dopacity are w.r.t. the raw values
+    const float* f_dc; const float* f_rest;      // split SH storage (then shs == nullptr) ...
+    float* dL_df_dc; float* dL_df_rest;          // ... and its gradients (P,1,3), (P,M-1,3) (then dL_dsh == nullptr)
 };
 size_t l1_ssim_blocks(int planes, int H, int W);
 void launch_l1_ssim_forward(const float* img, const float* gt, int planes, int H, int W, float lambda, float* dm_maps, float* partial,

@@ -12,6 +12,7 @@
 //   * the depth-sort key/value pair is emitted here.
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
+#include "gsr_fused_params.cuh"
 #include <stdio.h>
 
 namespace gsr {
@@ -46,6 +47,10 @@ __device__ __forceinline__ void sh_color_scalar(int K, const float* __restrict__
 }
 
 // 4 blocks per SM (64 registers): measured 0.194 -> 0.170 ms at C2 against the 85-register build
+// RAW  : opacities / scales / rotations hold the model's raw parameters; sigmoid / exp / normalize are applied here.
+// SPLIT: SH coefficients come from a.f_dc (P,1,3) and a.f_rest (P,M-1,3) instead of a.shs (P,M,3).
+// <false,false> is the reference-shaped path; the other instantiations are separate kernels, it is not touched by them.
+template <bool RAW, bool SPLIT>
 __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a) {
     __shared__ float s_cam[36];
     if (threadIdx.x < 16) s_cam[threadIdx.x] = a.cam.view[threadIdx.x];
@@ -74,7 +79,14 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
                                 __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
         sx_in = __ldg(a.scales + 3 * idx); sy_in = __ldg(a.scales + 3 * idx + 1); sz_in = __ldg(a.scales + 3 * idx + 2);
     }
-    const float opacity = __ldg(a.opacities + idx);
+    float opacity = __ldg(a.opacities + idx);
+    if (RAW) {
+        opacity = act_sigmoid(opacity);
+        if (a.cov3D_precomp == nullptr) {
+            sx_in = act_exp(sx_in); sy_in = act_exp(sy_in); sz_in = act_exp(sz_in);
+            q_in = act_normalize(q_in).q;
+        }
+    }
     // in_frustum (auxiliary.h:144-175): only the near-plane test is live
     const float depth = dot4(V[2], V[6], V[10], V[14], mx, my, mz);
     bool alive = in_range && !(depth <= 0.2f);
@@ -120,14 +132,26 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
                     const float x = __fdiv_rn(dx, len), y = __fdiv_rn(dy, len), z = __fdiv_rn(dz, len);
                     float k[16];
                     sh_basis(a.D, x, y, z, k);
+                    float res[3] = {0.f, 0.f, 0.f};
+                    if (SPLIT) {
+                        const float* dc = a.f_dc + 3 * (size_t)idx;
+                        const float* rest = a.f_rest + (size_t)idx * (a.M - 1) * 3;
+                        // aligned 16-byte reads start up to 3 floats before the row and end up to 3 floats after it:
+                        // inside the tensor for every Gaussian but the last one
+                        const bool vec_ok = ((reinterpret_cast<uintptr_t>(a.f_rest) & 15) == 0) && idx < a.P - 1;
+                        if (a.D == 3) sh_color_split<3>(dc, rest, vec_ok, k, res);
+                        else if (a.D == 2) sh_color_split<2>(dc, rest, vec_ok, k, res);
+                        else if (a.D == 1) sh_color_split<1>(dc, rest, vec_ok, k, res);
+                        else sh_color_split<0>(dc, rest, vec_ok, k, res);
+                    } else {
                     const float* sh = a.shs + (size_t)idx * a.M * 3;
                     const bool vec_ok = ((a.M * 3) % 4 == 0) && ((reinterpret_cast<uintptr_t>(a.shs) & 15) == 0);
-                    float res[3] = {0.f, 0.f, 0.f};
                     if (vec_ok && a.D == 3) sh_color_vec<3>(sh, k, res);
                     else if (vec_ok && a.D == 2 && a.M * 3 >= 28) sh_color_vec<2>(sh, k, res);
                     else if (vec_ok && a.D == 1) sh_color_vec<1>(sh, k, res);
                     else if (vec_ok && a.D == 0) sh_color_vec<0>(sh, k, res);
                     else sh_color_scalar((a.D + 1) * (a.D + 1), sh, k, res);
+                    }
 #pragma unroll
                     for (int ch = 0; ch < 3; ch++) {
                         const float v = addr(res[ch], 0.5f);
@@ -194,7 +218,12 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
 
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
-    preprocess_fwd_kernel<<<(a.P + 255) / 256, 256, 0, st>>>(a);
+    const unsigned nb = (unsigned)((a.P + 255) / 256);
+    const bool split = a.f_dc != nullptr;
+    if (!a.raw_act && !split) preprocess_fwd_kernel<false, false><<<nb, 256, 0, st>>>(a);
+    else if (a.raw_act && !split) preprocess_fwd_kernel<true, false><<<nb, 256, 0, st>>>(a);
+    else if (!a.raw_act && split) preprocess_fwd_kernel<false, true><<<nb, 256, 0, st>>>(a);
+    else preprocess_fwd_kernel<true, true><<<nb, 256, 0, st>>>(a);
     count_launch(1);
 }
 

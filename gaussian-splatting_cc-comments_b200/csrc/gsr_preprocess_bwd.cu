@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
+#include "gsr_fused_params.cuh"
 #include "gsr_smem.cuh"
 
 namespace gsr {
@@ -185,9 +186,12 @@ struct BwdIn {
     float4 q; float sx, sy, sz;
     uint32_t cl;
     bool vis;
+    // raw-parameter path only (RAW instantiations): what the activations' derivatives need
+    QuatNorm qn;          // normalisation of the raw quaternion (q holds the normalised one)
+    float op;             // activated opacity, from the forward's record
 };
 
-template <bool VEC>
+template <bool VEC, bool RAW, bool SPLIT>
 __device__ __forceinline__ void load_inputs(const PreprocessBwdArgs& a, int idx, bool vis, BwdIn& in) {
     in.vis = vis;
     in.g0 = in.g1 = in.q = make_float4(0, 0, 0, 0);
@@ -203,12 +207,18 @@ __device__ __forceinline__ void load_inputs(const PreprocessBwdArgs& a, int idx,
         else in.q = make_float4(__ldg(a.rotations + 4 * (size_t)idx), __ldg(a.rotations + 4 * (size_t)idx + 1),
                                 __ldg(a.rotations + 4 * (size_t)idx + 2), __ldg(a.rotations + 4 * (size_t)idx + 3));
         in.sx = __ldg(a.scales + i3); in.sy = __ldg(a.scales + i3 + 1); in.sz = __ldg(a.scales + i3 + 2);
+        if (RAW) {      // the forward's activations, same expressions (gsr_preprocess.cu)
+            in.sx = act_exp(in.sx); in.sy = act_exp(in.sy); in.sz = act_exp(in.sz);
+            in.qn = act_normalize(in.q);
+            in.q = in.qn.q;
+        }
     }
-    if (a.shs != nullptr) in.cl = a.clamped[idx];
+    if (RAW) in.op = reinterpret_cast<const float*>(a.packed + 3 * (size_t)idx + 1)[2];    // record b = (conic.z, thr, opacity, r)
+    if (SPLIT || a.shs != nullptr) in.cl = a.clamped[idx];
 }
 
 // Returns the number of SH coefficients written to dsh_row (0 when not visible or no SHs).
-template <bool SMEM>
+template <bool SMEM, bool RAW, bool SPLIT>
 __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, const BwdIn& in, const float* V, const float* Pm,
                                        const float* sh_row, float* dsh_row, BwdOut& o) {
 #pragma unroll
@@ -297,7 +307,7 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
     dmean[2] += (Pm[8] * m_w - Pm[11] * mul1) * g[0] + (Pm[9] * m_w - Pm[11] * mul2) * g[1];
     // ---- SH (backward.cu:392-394) ----
     int sh_written = 0;
-    if (a.shs != nullptr) {
+    if (SPLIT || a.shs != nullptr) {
         const uint32_t cl = in.cl;
         const F3 dRGB = f3((cl & 1) ? 0.f : g[6], (cl & 2) ? 0.f : g[7], (cl & 4) ? 0.f : g[8]);
         const F3 dir = f3(subr(mx, V[32]), subr(my, V[33]), subr(mz, V[34]));
@@ -319,6 +329,14 @@ __device__ __forceinline__ int bwd_one(const PreprocessBwdArgs& a, int idx, cons
     }
     // ---- scale / rotation (backward.cu:396-398) ----
     if (a.scales != nullptr) cov3d_backward(sx, sy, sz, a.scale_modifier, q, dcov, o.dscale, o.drot);
+    if (RAW) {      // chain rule through sigmoid / exp / normalize: the gradients leave w.r.t. the raw parameters
+        g[5] = act_sigmoid_bwd(in.op, g[5]);
+        if (a.scales != nullptr) {
+            o.dscale[0] = act_exp_bwd(sx, o.dscale[0]); o.dscale[1] = act_exp_bwd(sy, o.dscale[1]); o.dscale[2] = act_exp_bwd(sz, o.dscale[2]);
+            const float4 dr = act_normalize_bwd(in.qn, make_float4(o.drot[0], o.drot[1], o.drot[2], o.drot[3]));
+            o.drot[0] = dr.x; o.drot[1] = dr.y; o.drot[2] = dr.z; o.drot[3] = dr.w;
+        }
+    }
     return sh_written;
 }
 
@@ -329,6 +347,7 @@ __device__ __forceinline__ void load_camera(const PreprocessBwdArgs& a, float* s
 }
 
 // ---- generic kernel: any M, any alignment; per-thread strided stores ------------------------------------
+template <bool RAW>
 __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessBwdArgs a) {
     __shared__ float s_cam[36];
     load_camera(a, s_cam);
@@ -339,8 +358,8 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
     float* dsh = a.dL_dsh ? a.dL_dsh + (size_t)idx * a.M * 3 : nullptr;
     BwdOut o;
     BwdIn in;
-    load_inputs<false>(a, idx, a.radii[idx] > 0, in);
-    const int sh_written = bwd_one<false>(a, idx, in, s_cam, s_cam + 16, a.shs ? a.shs + (size_t)idx * a.M * 3 : nullptr, dsh, o);
+    load_inputs<false, RAW, false>(a, idx, a.radii[idx] > 0, in);
+    const int sh_written = bwd_one<false, RAW, false>(a, idx, in, s_cam, s_cam + 16, a.shs ? a.shs + (size_t)idx * a.M * 3 : nullptr, dsh, o);
     // ---- write everything (zeros where the reference's pre-zeroed tensors stay untouched) ----
     if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(o.g[2], o.g[3], 0.f, o.g[4]);
     a.dL_dcolor[i3] = o.g[6]; a.dL_dcolor[i3 + 1] = o.g[7]; a.dL_dcolor[i3 + 2] = o.g[8];
@@ -382,7 +401,8 @@ __device__ __forceinline__ void copy_out(float* __restrict__ dst, const float* _
     for (int i = 4 * n4 + threadIdx.x; i < n; i += PB) dst[i] = src[i];
 }
 
-template <int MINB, bool PACK>
+// RAW / SPLIT: the raw-parameter path (gsr_fused_params.cuh); <.., false, false> are the reference-shaped kernels.
+template <int MINB, bool PACK, bool RAW, bool SPLIT>
 __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(PreprocessBwdArgs a, int S /* smem row stride, floats */) {
     __shared__ float s_cam[36];
     __shared__ uint8_t s_vis[PB];
@@ -399,13 +419,19 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
     s_vis[t] = vis;
     __syncthreads();
     BwdIn in;
-    load_inputs<true>(a, idx, vis, in);
+    load_inputs<true, RAW, SPLIT>(a, idx, vis, in);
     const int L = 3 * a.M;
     const int Kf = 3 * (a.D + 1) * (a.D + 1);               // live floats per row
     const int Kf4 = (Kf + 3) & ~3;
-    const bool has_sh = a.shs != nullptr;
+    const bool has_sh = SPLIT || a.shs != nullptr;
     const int qstep = L ? (4 * PB) / L : 0, rstep = L ? (4 * PB) % L : 0;
-    if (has_sh) {
+    if (SPLIT) {
+        // rows [dc(3) | rest]: only the rest part is read by the backward (the DC coefficient has no direction derivative)
+        stage_rest_rows<PB>(s_sh, S, a.f_rest + (size_t)row0 * (L - 3), nrows, L - 3, Kf - 3, s_vis, t);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+    } else if (has_sh) {
         const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)row0 * L);
         const int n4 = nrows * L / 4;
         int f = 4 * t, row = f / L, col = f - row * L;
@@ -425,10 +451,12 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
     BwdOut o;
     if (valid) {
         float* myrow = s_sh + t * S;
-        bwd_one<true>(a, idx, in, s_cam, s_cam + 16, myrow, myrow, o);
+        bwd_one<true, RAW, SPLIT>(a, idx, in, s_cam, s_cam + 16, myrow, myrow, o);
     }
     __syncthreads();
-    if (a.dL_dsh != nullptr && L > 0 && !a.skip_dsh) {
+    if (SPLIT) {
+        store_split_rows<PB>(s_sh, S, a.dL_df_dc + (size_t)row0 * 3, a.dL_df_rest + (size_t)row0 * (L - 3), nrows, L - 3, Kf, s_vis, t);
+    } else if (a.dL_dsh != nullptr && L > 0 && !a.skip_dsh) {
         float4* dst = reinterpret_cast<float4*>(a.dL_dsh + (size_t)row0 * L);
         const int n4 = nrows * L / 4;
         int f = 4 * t, row = f / L, col = f - row * L;
@@ -488,6 +516,17 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     const bool aligned = (reinterpret_cast<uintptr_t>(a.shs) & 15) == 0 && (reinterpret_cast<uintptr_t>(a.dL_dsh) & 15) == 0 &&
                          (reinterpret_cast<uintptr_t>(a.rotations) & 15) == 0;
     const bool staged = (L % 4 == 0) && aligned && dyn <= 40 * 1024 && (a.M == 0 || a.dL_dsh != nullptr);
+    if (a.f_dc != nullptr) {
+        // split SH storage: always staged (rows are filled with 4-byte copies, so any M works); gsr_backward has checked
+        // M <= 16, the alignment of `rotations` and that no exchange option is combined with it
+        const int S4 = (L + 3) / 4, Ss = 4 * (S4 % 2 == 1 ? S4 : S4 + 1);        // odd number of 16-byte words per row
+        size_t dyns = (size_t)PB_OUT * sizeof(float);
+        if ((size_t)PB * Ss * sizeof(float) > dyns) dyns = (size_t)PB * Ss * sizeof(float);
+        if (a.raw_act) preprocess_bwd_kernel_staged<8, false, true, true><<<(a.P + PB - 1) / PB, PB, dyns, st>>>(a, Ss);
+        else preprocess_bwd_kernel_staged<8, false, false, true><<<(a.P + PB - 1) / PB, PB, dyns, st>>>(a, Ss);
+        count_launch(1);
+        return;
+    }
     // beside a collective (multi-view exchange): chunked, see chunk_plan
     int bounds[5];
     const int nchunk = a.chunked ? chunk_plan(a.P, 256, bounds) : 1;
@@ -497,9 +536,11 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
         ac.begin = bounds[c]; ac.P = bounds[c + 1];
         const int n = ac.P - ac.begin;
         if (n <= 0) continue;
-        if (staged && a.small_pack) preprocess_bwd_kernel_staged<8, true><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
-        else if (staged) preprocess_bwd_kernel_staged<8, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
-        else preprocess_bwd_kernel_generic<<<(n + 255) / 256, 256, 0, st>>>(ac);
+        if (staged && a.small_pack) preprocess_bwd_kernel_staged<8, true, false, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        else if (staged && a.raw_act) preprocess_bwd_kernel_staged<8, false, true, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        else if (staged) preprocess_bwd_kernel_staged<8, false, false, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        else if (a.raw_act) preprocess_bwd_kernel_generic<true><<<(n + 255) / 256, 256, 0, st>>>(ac);
+        else preprocess_bwd_kernel_generic<false><<<(n + 255) / 256, 256, 0, st>>>(ac);
         count_launch(1);
         if (a.chunk_events && c < a.n_chunk_events && c < nchunk - 1) cudaEventRecord((cudaEvent_t)a.chunk_events[c], st);
     }

@@ -159,6 +159,107 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
     return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
 }
 
+// ---- raw-parameter path (include/gsr.h: raw_activations / features_dc / features_rest) ----
+// The model's tensors as GaussianModel stores them (scene/gaussian_model.py:44-50): _xyz, _features_dc (P,1,3),
+// _features_rest (P,M-1,3), _opacity (logits), _scaling (log), _rotation (unnormalised).  Same outputs as
+// rasterize_gaussians; the backward returns the gradients w.r.t. these raw tensors.
+std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+RasterizeGaussiansRawCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& features_dc,
+                          const torch::Tensor& features_rest, const torch::Tensor& raw_opacity, const torch::Tensor& raw_scaling,
+                          const torch::Tensor& raw_rotation, const float scale_modifier, const torch::Tensor& viewmatrix,
+                          const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy, const int image_height,
+                          const int image_width, const int degree, const torch::Tensor& campos, const bool prefiltered, const bool debug) {
+    if (means3D.ndimension() != 2 || means3D.size(1) != 3) AT_ERROR("means3D must have dimensions (num_points, 3)");
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const auto dev = means3D.device();
+    const int64_t P = means3D.size(0);
+    const int H = image_height, W = image_width;
+    TORCH_CHECK(features_dc.dim() == 3 && features_dc.size(0) == P && features_dc.size(1) == 1 && features_dc.size(2) == 3, "features_dc must be (P,1,3)");
+    TORCH_CHECK(features_rest.dim() == 3 && features_rest.size(0) == P && features_rest.size(2) == 3, "features_rest must be (P,M-1,3)");
+    TORCH_CHECK(raw_opacity.numel() == P && raw_scaling.numel() == 3 * P && raw_rotation.numel() == 4 * P, "opacity (P,1), scaling (P,3), rotation (P,4)");
+    auto fopt = means3D.options().dtype(torch::kFloat32);
+    torch::Tensor out_color = P == 0 ? torch::zeros({3, H, W}, fopt) : torch::empty({3, H, W}, fopt);
+    torch::Tensor radii = torch::empty({P}, means3D.options().dtype(torch::kInt32));
+    auto bopt = torch::TensorOptions().dtype(torch::kByte).device(dev);
+    torch::Tensor geomBuffer = torch::empty({0}, bopt), binningBuffer = torch::empty({0}, bopt), imgBuffer = torch::empty({0}, bopt);
+    int rendered = 0;
+    if (P != 0) {
+        auto bg = prep(background, dev, "bg"), m3 = prep(means3D, dev, "means3D"), dc = prep(features_dc, dev, "features_dc"),
+             rest = prep(features_rest, dev, "features_rest"), op = prep(raw_opacity, dev, "opacity"), sc = prep(raw_scaling, dev, "scaling"),
+             rot = prep(raw_rotation, dev, "rotation"), vm = prep(viewmatrix, dev, "viewmatrix"), pm = prep(projmatrix, dev, "projmatrix"),
+             cp = prep(campos, dev, "campos");
+        gsr_forward_args a{};
+        a.P = (int)P; a.D = degree; a.M = 1 + (int)features_rest.size(1);
+        a.background = fptr(bg); a.width = W; a.height = H;
+        a.means3D = fptr(m3); a.opacities = fptr(op); a.scales = fptr(sc); a.scale_modifier = scale_modifier; a.rotations = fptr(rot);
+        a.viewmatrix = fptr(vm); a.projmatrix = fptr(pm); a.cam_pos = fptr(cp);
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.prefiltered = prefiltered;
+        a.out_color = out_color.data_ptr<float>(); a.radii = radii.data_ptr<int>(); a.debug = debug;
+        a.raw_activations = 1; a.features_dc = fptr(dc); a.features_rest = fptr(rest);
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(gsr_forward(&a, resize_cb, &geomBuffer, resize_cb, &binningBuffer, resize_cb, &imgBuffer, (void*)st, &rendered));
+    }
+    return std::make_tuple(rendered, out_color, radii, geomBuffer, binningBuffer, imgBuffer);
+}
+
+// -> (dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_dfeatures_dc, dL_dfeatures_rest, dL_dscaling, dL_drotation), all w.r.t. the raw tensors
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>
+RasterizeGaussiansRawBackwardCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                                  const torch::Tensor& features_dc, const torch::Tensor& features_rest, const torch::Tensor& raw_scaling,
+                                  const torch::Tensor& raw_rotation, const float scale_modifier, const torch::Tensor& viewmatrix,
+                                  const torch::Tensor& projmatrix, const float tan_fovx, const float tan_fovy,
+                                  const torch::Tensor& dL_dout_color, const int degree, const torch::Tensor& campos,
+                                  const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer,
+                                  const torch::Tensor& imageBuffer, const bool debug) {
+    TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    const auto dev = means3D.device();
+    const int64_t P = means3D.size(0);
+    const int H = dL_dout_color.size(1), W = dL_dout_color.size(2);
+    const int64_t Mr = features_rest.size(1);
+    auto fopt = means3D.options().dtype(torch::kFloat32);
+    // one flat arena as in rasterize_gaussians_backward: the live blocks first, then the ones training never reads
+    const int64_t widths[10] = {3, 3, 1, 3, 4, 3, 3 * Mr, 3, 6, 4};
+    int64_t offs[11]; offs[0] = 0;
+    for (int i = 0; i < 10; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;
+    torch::Tensor flat = torch::empty({offs[10]}, fopt);
+    auto view = [&](int i, std::vector<int64_t> shape) { return flat.narrow(0, offs[i], widths[i] * P).view(shape); };
+    torch::Tensor dL_dmeans3D = view(0, {P, 3}), dL_dmeans2D = view(1, {P, 3}), dL_dopacity = view(2, {P, 1}),
+                  dL_dscales = view(3, {P, 3}), dL_drotations = view(4, {P, 4}), dL_ddc = view(5, {P, 1, 3}),
+                  dL_drest = view(6, {P, Mr, 3}), dL_dcolors = view(7, {P, 3}), dL_dcov3D = view(8, {P, 6}), dL_dconic = view(9, {P, 2, 2});
+    if (P != 0) {
+        auto bg = prep(background, dev, "bg"), m3 = prep(means3D, dev, "means3D"), dc = prep(features_dc, dev, "features_dc"),
+             rest = prep(features_rest, dev, "features_rest"), sc = prep(raw_scaling, dev, "scaling"), rot = prep(raw_rotation, dev, "rotation"),
+             vm = prep(viewmatrix, dev, "viewmatrix"), pm = prep(projmatrix, dev, "projmatrix"), cp = prep(campos, dev, "campos"),
+             dpix = prep(dL_dout_color, dev, "dL_dout_color");
+        auto rad = radii.contiguous();
+        torch::Tensor scratch = torch::empty({(int64_t)gsr_backward_scratch_bytes((int)P)}, torch::TensorOptions().dtype(torch::kByte).device(dev));
+        gsr_backward_args a{};
+        a.P = (int)P; a.D = degree; a.M = 1 + (int)Mr; a.R = R;
+        a.background = fptr(bg); a.width = W; a.height = H;
+        a.means3D = fptr(m3); a.scales = fptr(sc); a.scale_modifier = scale_modifier; a.rotations = fptr(rot);
+        a.viewmatrix = fptr(vm); a.projmatrix = fptr(pm); a.cam_pos = fptr(cp);
+        a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy;
+        a.radii = rad.data_ptr<int>();
+        a.geom_buffer = reinterpret_cast<const char*>(geomBuffer.data_ptr());
+        a.binning_buffer = reinterpret_cast<const char*>(binningBuffer.data_ptr());
+        a.image_buffer = reinterpret_cast<const char*>(imageBuffer.data_ptr());
+        a.dL_dpix = fptr(dpix);
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dconic = dL_dconic.data_ptr<float>();
+        a.dL_dopacity = dL_dopacity.data_ptr<float>(); a.dL_dcolor = dL_dcolors.data_ptr<float>();
+        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dcov3D = dL_dcov3D.data_ptr<float>();
+        a.dL_dscale = dL_dscales.data_ptr<float>(); a.dL_drot = dL_drotations.data_ptr<float>();
+        a.grad_scratch = reinterpret_cast<float*>(scratch.data_ptr());
+        a.debug = debug;
+        a.raw_activations = 1; a.features_dc = fptr(dc); a.features_rest = fptr(rest);
+        a.dL_dfeatures_dc = dL_ddc.data_ptr<float>(); a.dL_dfeatures_rest = Mr > 0 ? dL_drest.data_ptr<float>() : nullptr;
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(gsr_backward(&a, (void*)st));
+    }
+    return std::make_tuple(dL_dmeans2D, dL_dopacity, dL_dmeans3D, dL_ddc, dL_drest, dL_dscales, dL_drotations);
+}
+
 torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
     TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (there is no CPU path)");
     const c10::cuda::CUDAGuard guard(means3D.device());
@@ -218,6 +319,14 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
           py::arg("tile_row_end") = 0, py::arg("drgb_block") = py::none(), py::arg("skip_dsh") = false,
           py::arg("drgb_event") = 0, py::arg("chunk_events") = std::vector<int64_t>(),
           py::arg("small_pack") = py::none());
+    m.def("rasterize_gaussians_raw", &RasterizeGaussiansRawCUDA, py::arg("background"), py::arg("means3D"), py::arg("features_dc"),
+          py::arg("features_rest"), py::arg("opacity"), py::arg("scaling"), py::arg("rotation"), py::arg("scale_modifier"), py::arg("viewmatrix"),
+          py::arg("projmatrix"), py::arg("tan_fovx"), py::arg("tan_fovy"), py::arg("image_height"), py::arg("image_width"), py::arg("degree"),
+          py::arg("campos"), py::arg("prefiltered"), py::arg("debug"));
+    m.def("rasterize_gaussians_raw_backward", &RasterizeGaussiansRawBackwardCUDA, py::arg("background"), py::arg("means3D"), py::arg("radii"),
+          py::arg("features_dc"), py::arg("features_rest"), py::arg("scaling"), py::arg("rotation"), py::arg("scale_modifier"),
+          py::arg("viewmatrix"), py::arg("projmatrix"), py::arg("tan_fovx"), py::arg("tan_fovy"), py::arg("dL_dout_color"), py::arg("degree"),
+          py::arg("campos"), py::arg("geomBuffer"), py::arg("R"), py::arg("binningBuffer"), py::arg("imageBuffer"), py::arg("debug"));
     m.def("unpack_small_grads", [](int64_t begin, int64_t end, const torch::Tensor& pack, torch::Tensor& dmean3D, torch::Tensor& dmean2D,
                                    torch::Tensor& dop, torch::Tensor& dscale, torch::Tensor& drot) {
         TORCH_CHECK(pack.is_cuda() && pack.is_contiguous() && pack.scalar_type() == torch::kFloat32, "pack: contiguous float32 CUDA tensor");

@@ -104,6 +104,43 @@ class _RasterizeGaussians(torch.autograd.Function):
                 grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
 
 
+# ---- raw-parameter path (extension) ---------------------------------------------------------
+def rasterize_gaussians_raw(means3D, means2D, features_dc, features_rest, raw_opacities, raw_scales, raw_rotations,
+                            raster_settings):
+    return _RasterizeGaussiansRaw.apply(means3D, means2D, features_dc, features_rest, raw_opacities, raw_scales,
+                                        raw_rotations, raster_settings)
+
+
+class _RasterizeGaussiansRaw(torch.autograd.Function):
+    """_RasterizeGaussians on the model's RAW tensors: sigmoid / exp / normalize and the SH concatenation that
+    gaussian_renderer/__init__.py:69-101 performs with torch kernels before the rasterizer (and autograd after it) happen
+    inside the per-Gaussian kernels.  Gradients come back w.r.t. the raw tensors."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, features_dc, features_rest, raw_opacities, raw_scales, raw_rotations, raster_settings):
+        rs = raster_settings
+        if _band(rs) != (0, 0) or _multiview is not None:
+            raise Exception("the raw-parameter path is single-GPU, full-image (use GaussianRasterizer.forward for bands / multi-view)")
+        out = _C.rasterize_gaussians_raw(rs.bg, means3D, features_dc, features_rest, raw_opacities, raw_scales, raw_rotations,
+                                         rs.scale_modifier, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height,
+                                         rs.image_width, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
+        num_rendered, color, radii, geomBuffer, binningBuffer, imgBuffer = out
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.save_for_backward(means3D, features_dc, features_rest, raw_scales, raw_rotations, radii, geomBuffer, binningBuffer, imgBuffer)
+        ctx.mark_non_differentiable(radii)
+        return color, radii
+
+    @staticmethod
+    def backward(ctx, grad_out_color, _):
+        rs = ctx.raster_settings
+        means3D, features_dc, features_rest, raw_scales, raw_rotations, radii, geomBuffer, binningBuffer, imgBuffer = ctx.saved_tensors
+        (grad_means2D, grad_opacities, grad_means3D, grad_dc, grad_rest, grad_scales, grad_rotations) = _C.rasterize_gaussians_raw_backward(
+            rs.bg, means3D, radii, features_dc, features_rest, raw_scales, raw_rotations, rs.scale_modifier, rs.viewmatrix, rs.projmatrix,
+            rs.tanfovx, rs.tanfovy, grad_out_color, rs.sh_degree, rs.campos, geomBuffer, ctx.num_rendered, binningBuffer, imgBuffer, rs.debug)
+        return grad_means3D, grad_means2D, grad_dc, grad_rest, grad_opacities, grad_scales, grad_rotations, None
+
+
 class GaussianRasterizationSettings(NamedTuple):
     image_height: int
     image_width: int
@@ -144,3 +181,9 @@ class GaussianRasterizer(nn.Module):
         cov3D_precomp = empty if cov3D_precomp is None else cov3D_precomp
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
                                    cov3D_precomp, self.raster_settings)
+
+    def forward_raw(self, means3D, means2D, features_dc, features_rest, raw_opacities, raw_scales, raw_rotations):
+        """Extension: the model's raw tensors (`_features_dc`, `_features_rest`, `_opacity`, `_scaling`, `_rotation` of
+        scene/gaussian_model.py:44-50) instead of activated ones; same (color, radii).  See gsr_render.render."""
+        return rasterize_gaussians_raw(means3D, means2D, features_dc, features_rest, raw_opacities, raw_scales, raw_rotations,
+                                       self.raster_settings)

@@ -70,6 +70,16 @@ typedef struct gsr_forward_args {
      * [tile_row_begin, tile_row_end) for tile-row sharded multi-GPU rendering.  0,0 = all rows.
      * radii are computed on the full image either way. */
     int tile_row_begin, tile_row_end;
+    /* Extension (not in the reference): the model's RAW parameters, as GaussianModel stores them,
+     * instead of the activated tensors gaussian_renderer/__init__.py:69-101 builds with separate torch kernels.
+     * raw_activations != 0: `opacities` holds logits (sigmoid applied here, scene/gaussian_model.py:128-130), `scales`
+     *   log-scales (exp, :114-117), `rotations` unnormalised quaternions (F.normalize, eps 1e-12, :119-122).
+     * features_dc != NULL: SH coefficients in split storage -- features_dc (P,1,3) and features_rest (P,M-1,3), the two
+     *   tensors `get_features` concatenates (:132-138); then shs and colors_precomp must be NULL and M is the total
+     *   coefficient count.  The two options are independent.  Zero / NULL = the reference's interface. */
+    int raw_activations;
+    const float* features_dc;
+    const float* features_rest;
 } gsr_forward_args;
 
 typedef struct gsr_backward_args {
@@ -130,6 +140,16 @@ typedef struct gsr_backward_args {
      * 56-byte row INSTEAD of into their five tensors, so that a range of Gaussians is one contiguous span for
      * the cross-rank reduction; gsr_unpack_small_grads then scatters reduced rows into the five tensors. */
     float* small_pack;
+    /* Raw-parameter path, as in gsr_forward_args (same values as the forward call).  With raw_activations the gradients
+     * dL_dopacity / dL_dscale / dL_drot are w.r.t. the RAW parameters (sigmoid / exp / normalize derivatives applied here).
+     * With features_dc set, the SH gradient is written as dL_dfeatures_dc (P,1,3) and dL_dfeatures_rest (P,M-1,3) -- what
+     * torch.cat's backward would copy out of dL_dsh -- and shs / dL_dsh must be NULL; M <= 16.  Not combined with dL_drgb /
+     * small_pack. */
+    int raw_activations;
+    const float* features_dc;
+    const float* features_rest;
+    float* dL_dfeatures_dc;
+    float* dL_dfeatures_rest;
 } gsr_backward_args;
 #define GSR_SMALL_PACK_FLOATS 14
 

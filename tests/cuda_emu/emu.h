@@ -103,6 +103,17 @@ inline float __fadd_rn(float a, float b) { volatile float r = a + b; return r; }
 inline float __fsub_rn(float a, float b) { volatile float r = a - b; return r; }
 inline float __fdiv_rn(float a, float b) { volatile float r = a / b; return r; }
 inline float __fsqrt_rn(float a) { return std::sqrt(a); }
+inline double __dadd_rn(double a, double b) { volatile double r = a + b; return r; }
+inline double __dmul_rn(double a, double b) { volatile double r = a * b; return r; }
+inline double __fma_rn(double a, double b, double c) { return std::fma(a, b, c); }
+inline float __double2float_rn(double a) { return (float)a; }
+inline float __int2float_rn(int a) { return (float)a; }
+inline int __float2int_rz(float f) {               // cvt.rzi.s32.f32: NaN -> 0, saturating
+    if (!(f == f)) return 0;
+    if (f >= 2147483648.f) return 2147483647;
+    if (f <= -2147483648.f) return -2147483647 - 1;
+    return (int)f;
+}
 inline unsigned __float2uint_rz(float f) {          // cvt.rzi.u32.f32: NaN -> 0, saturating
     if (!(f == f) || f <= 0.f) return 0u;
     if (f >= 4294967296.f) return 0xFFFFFFFFu;

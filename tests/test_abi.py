@@ -78,7 +78,22 @@ class FwdArgs(C.Structure):
                 ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p),
                 ("projmatrix", C.c_void_p), ("cam_pos", C.c_void_p), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float),
                 ("prefiltered", C.c_int), ("out_color", C.c_void_p), ("radii", C.c_void_p), ("debug", C.c_int),
-                ("tile_row_begin", C.c_int), ("tile_row_end", C.c_int)]
+                ("tile_row_begin", C.c_int), ("tile_row_end", C.c_int),
+                ("raw_activations", C.c_int), ("features_dc", C.c_void_p), ("features_rest", C.c_void_p)]
+
+
+class BwdArgs(C.Structure):
+    _fields_ = [("P", C.c_int), ("D", C.c_int), ("M", C.c_int), ("R", C.c_int), ("background", C.c_void_p), ("width", C.c_int),
+                ("height", C.c_int), ("means3D", C.c_void_p), ("shs", C.c_void_p), ("colors_precomp", C.c_void_p), ("scales", C.c_void_p),
+                ("scale_modifier", C.c_float), ("rotations", C.c_void_p), ("cov3D_precomp", C.c_void_p), ("viewmatrix", C.c_void_p),
+                ("projmatrix", C.c_void_p), ("cam_pos", C.c_void_p), ("tan_fovx", C.c_float), ("tan_fovy", C.c_float), ("radii", C.c_void_p),
+                ("geom_buffer", C.c_void_p), ("binning_buffer", C.c_void_p), ("image_buffer", C.c_void_p), ("dL_dpix", C.c_void_p),
+                ("dL_dmean2D", C.c_void_p), ("dL_dconic", C.c_void_p), ("dL_dopacity", C.c_void_p), ("dL_dcolor", C.c_void_p),
+                ("dL_dmean3D", C.c_void_p), ("dL_dcov3D", C.c_void_p), ("dL_dsh", C.c_void_p), ("dL_dscale", C.c_void_p), ("dL_drot", C.c_void_p),
+                ("grad_scratch", C.c_void_p), ("debug", C.c_int), ("tile_row_begin", C.c_int), ("tile_row_end", C.c_int),
+                ("dL_drgb", C.c_void_p), ("skip_dL_dsh", C.c_int), ("drgb_ready_event", C.c_void_p), ("chunk_done_events", C.c_void_p),
+                ("n_chunk_events", C.c_int), ("small_pack", C.c_void_p), ("raw_activations", C.c_int), ("features_dc", C.c_void_p),
+                ("features_rest", C.c_void_p), ("dL_dfeatures_dc", C.c_void_p), ("dL_dfeatures_rest", C.c_void_p)]
 
 
 RESIZE = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
@@ -123,6 +138,54 @@ def test_mark_visible_argument_checks(lib):
 
 def test_backward_argument_checks(lib):
     assert lib.gsr_backward(None, None) == 1
+
+
+def _fill(args, names, value=0x1000):
+    for n in names:
+        setattr(args, n, value)
+
+
+def test_raw_parameter_path_argument_checks(lib):
+    """Split SH storage and raw activations are validated on the host before any launch."""
+    lib.gsr_last_error.restype = C.c_char_p
+    a = FwdArgs()
+    a.P, a.width, a.height, a.M, a.D = 10, 16, 16, 16, 3
+    _fill(a, ["means3D", "opacities", "viewmatrix", "projmatrix", "cam_pos", "background", "out_color", "scales", "rotations"])
+    a.features_dc = 0x1000                       # features_rest missing although M > 1
+    rc, _, msg = _call_forward(lib, a)
+    assert rc == 1 and "split SH" in msg
+    a.features_rest = 0x1000
+    a.shs = 0x1000                               # both layouts at once
+    rc, _, msg = _call_forward(lib, a)
+    assert rc == 1 and "split SH" in msg
+    a.shs = None
+    a.D = 4                                      # degree does not fit
+    rc, _, msg = _call_forward(lib, a)
+    assert rc == 1 and "degree" in msg
+
+    b = BwdArgs()
+    b.P, b.width, b.height, b.M, b.D, b.R = 10, 16, 16, 16, 3, 0
+    _fill(b, ["means3D", "radii", "geom_buffer", "binning_buffer", "image_buffer", "dL_dpix", "viewmatrix", "projmatrix", "cam_pos",
+              "background", "grad_scratch", "dL_dmean2D", "dL_dopacity", "dL_dcolor", "dL_dmean3D", "dL_dcov3D", "dL_dscale", "dL_drot",
+              "scales", "rotations"])
+    assert lib.gsr_backward(C.byref(b), None) == 1 and b"output pointer" in lib.gsr_last_error()      # M > 0 and no dL_dsh
+    b.features_dc = b.features_rest = 0x1000
+    assert lib.gsr_backward(C.byref(b), None) == 1 and b"split SH" in lib.gsr_last_error()            # gradients of the split tensors missing
+    b.dL_dfeatures_dc = b.dL_dfeatures_rest = 0x1000
+    b.M = 25
+    assert lib.gsr_backward(C.byref(b), None) == 1 and b"split SH" in lib.gsr_last_error()            # M <= 16
+    b.M = 16
+    b.rotations = 0x1004
+    assert lib.gsr_backward(C.byref(b), None) == 1 and b"aligned" in lib.gsr_last_error()
+    b.rotations = 0x1000
+    b.small_pack = 0x1000
+    assert lib.gsr_backward(C.byref(b), None) == 1 and b"multi-view" in lib.gsr_last_error()
+    b.small_pack = None
+    b.features_dc = b.features_rest = b.dL_dfeatures_dc = b.dL_dfeatures_rest = None
+    b.dL_dsh = 0x1000
+    b.raw_activations = 1
+    b.dL_drgb = 0x1000
+    assert lib.gsr_backward(C.byref(b), None) == 1 and b"multi-view" in lib.gsr_last_error()
 
 
 def test_backward_chunk_plan_covers_every_gaussian_once(lib):

@@ -16,6 +16,7 @@ from oracle import gs_next_oracle as O
 HERE = os.path.dirname(os.path.abspath(__file__))
 EMU_DIR = os.path.join(HERE, "cuda_emu")
 SO = os.path.join(EMU_DIR, "libemu_next.so")
+SO_FUSED = os.path.join(EMU_DIR, "libemu_fused.so")
 CSRC = os.path.join(os.path.dirname(HERE), "gaussian-splatting_cc-comments_b200", "csrc")
 
 
@@ -31,6 +32,17 @@ def emu():
     lib.emu_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
     lib.emu_adam_step.argtypes = [C.c_int] + [C.c_void_p] * 8 + [C.c_double] * 3 + [C.c_void_p, C.c_int]
     return lib
+
+
+@pytest.fixture(scope="module")
+def emu_fused():
+    deps = [os.path.join(EMU_DIR, "emu_fused.cpp"), os.path.join(EMU_DIR, "emu.h"), os.path.join(CSRC, "gsr_fused_params.cuh"),
+            os.path.join(CSRC, "gsr_math.cuh")]
+    if not os.path.exists(SO_FUSED) or any(os.path.getmtime(SO_FUSED) < os.path.getmtime(d) for d in deps):
+        r = subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-fPIC", "-shared", "-ffp-contract=off", "-mfma", "-w",
+                            "-I/usr/local/cuda/include", deps[0], "-o", SO_FUSED], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-3000:]
+    return C.CDLL(SO_FUSED)
 
 
 def _knn(lib, pts):
@@ -131,3 +143,89 @@ def test_adam_kernel_visibility_mask_leaves_rows_untouched(emu):
         rows = np.repeat(vis.astype(bool), r["w"])
         for k in "pmv":
             assert np.array_equal(g[k], np.where(rows, r[k], before[k])), k
+
+
+# ------------------------------------------------------------------ raw-parameter helpers (csrc/gsr_fused_params.cuh)
+def _aligned(n, dtype=np.float32, offset_floats=0):
+    raw = np.zeros(n + 8 + offset_floats, dtype)
+    start = (-raw.ctypes.data // 4) % 4                      # floats to the next 16-byte boundary
+    return raw[start + offset_floats:start + offset_floats + n]
+
+
+@pytest.mark.parametrize("M,D", [(16, 3), (16, 2), (16, 1), (16, 0), (9, 2), (4, 1), (2, 0), (1, 0)])
+def test_split_sh_colour_equals_the_concatenated_layout(emu_fused, M, D):
+    """Every row phase (rest rows are 12*(M-1) bytes apart: four alignments), vector and scalar path bit-identical, and
+    equal to the dot product over the concatenated (P,M,3) tensor."""
+    rng = np.random.default_rng(M * 10 + D)
+    P = 41
+    dc = _aligned(3 * P); dc[:] = rng.normal(size=3 * P)
+    rest = _aligned(max(1, 3 * (M - 1) * P)); rest[:] = rng.normal(size=rest.size)
+    k = np.ascontiguousarray(rng.normal(size=(P, 16)).astype(np.float32))
+    out_v = np.zeros((P, 3), np.float32); out_s = np.zeros((P, 3), np.float32)
+    args = lambda o, vec: (P, M, D, dc.ctypes.data_as(C.c_void_p), rest.ctypes.data_as(C.c_void_p), k.ctypes.data_as(C.c_void_p),
+                           o.ctypes.data_as(C.c_void_p), vec)
+    emu_fused.emu_sh_color_split(*args(out_v, 1))
+    emu_fused.emu_sh_color_split(*args(out_s, 0))
+    assert np.array_equal(out_v, out_s)
+    K = (D + 1) ** 2
+    shs = np.concatenate([dc.reshape(P, 1, 3), rest[:3 * (M - 1) * P].reshape(P, M - 1, 3)], axis=1).astype(np.float64)
+    want = (shs[:, :K, :] * k[:, :K, None].astype(np.float64)).sum(axis=1)
+    assert np.abs(out_v - want).max() <= 1e-5
+
+
+@pytest.mark.parametrize("M,D,nrows", [(16, 3, 128), (16, 3, 77), (16, 1, 128), (9, 2, 128), (4, 1, 5), (2, 0, 128), (16, 0, 31)])
+def test_backward_staging_and_split_write_out_index_maps(emu_fused, M, D, nrows):
+    rng = np.random.default_rng(M + D + nrows)
+    Lr, K = 3 * (M - 1), (D + 1) ** 2
+    L = 3 * M
+    S4 = (L + 3) // 4
+    S = 4 * (S4 if S4 % 2 == 1 else S4 + 1)
+    vis = (rng.random(128) < 0.7).astype(np.uint8)
+    rest_block = _aligned(max(1, nrows * Lr)); rest_block[:] = rng.normal(size=rest_block.size)
+    rows = np.full((128, S), np.nan, np.float32)
+    emu_fused.emu_stage_rest_rows(nrows, M, 3 * K - 3, S, vis.ctypes.data_as(C.c_void_p), rest_block.ctypes.data_as(C.c_void_p),
+                                  rows.ctypes.data_as(C.c_void_p))
+    want = np.full((128, S), np.nan, np.float32)
+    src = rest_block[:nrows * Lr].reshape(nrows, Lr)
+    for r in range(nrows):
+        if vis[r]:
+            want[r, 3:3 + 3 * K - 3] = src[r, :3 * K - 3]
+    assert np.array_equal(np.isnan(rows), np.isnan(want)) and np.array_equal(np.nan_to_num(rows), np.nan_to_num(want))
+    # write-out: rows now hold dL_dsh[0..3K) (anything beyond is NOT to be trusted: poison it)
+    rows = rng.normal(size=(128, S)).astype(np.float32)
+    rows[:, 3 * K:] = np.nan
+    for misalign in (0, 1):
+        dc_out = _aligned(3 * nrows); dc_out[:] = -7
+        rest_out = _aligned(max(1, nrows * Lr), offset_floats=misalign); rest_out[:] = -7
+        emu_fused.emu_store_split_rows(nrows, M, 3 * K, S, vis.ctypes.data_as(C.c_void_p), rows.ctypes.data_as(C.c_void_p),
+                                       dc_out.ctypes.data_as(C.c_void_p), rest_out.ctypes.data_as(C.c_void_p))
+        v = vis[:nrows].astype(bool)
+        assert np.array_equal(dc_out.reshape(nrows, 3), np.where(v[:, None], rows[:nrows, :3], 0.0))
+        want_rest = np.zeros((nrows, Lr), np.float32)
+        want_rest[:, :3 * K - 3] = np.where(v[:, None], rows[:nrows, 3:3 * K], 0.0)
+        assert np.array_equal(rest_out[:nrows * Lr].reshape(nrows, Lr), want_rest), (misalign,)
+
+
+def test_activations_and_their_derivatives_match_torch(emu_fused):
+    import torch
+    g = torch.Generator().manual_seed(0)
+    n = 500
+    raw_op = (torch.randn(n, generator=g) * 3).requires_grad_(True)
+    raw_s = (torch.randn(n, 3, generator=g) * 2 - 3).requires_grad_(True)
+    raw_q = torch.randn(n, 4, generator=g) * 10.0 ** torch.randint(-3, 3, (n, 1), generator=g).float()
+    raw_q[0] = 0.0                                          # below eps: F.normalize clamps the denominator
+    raw_q.requires_grad_(True)
+    g_op, g_s, g_q = torch.randn(n, generator=g), torch.randn(n, 3, generator=g), torch.randn(n, 4, generator=g)
+    op, s, q = torch.sigmoid(raw_op), torch.exp(raw_s), torch.nn.functional.normalize(raw_q)
+    ((op * g_op).sum() + (s * g_s).sum() + (q * g_q).sum()).backward()
+    outs = [np.zeros(x, np.float32) for x in (n, 3 * n, 4 * n, n, 3 * n, 4 * n)]
+    p = lambda a: np.ascontiguousarray(a.detach().numpy()).ctypes.data_as(C.c_void_p)
+    keep = [np.ascontiguousarray(t.detach().numpy()) for t in (raw_op, raw_s, raw_q, g_op, g_s, g_q)]
+    emu_fused.emu_activations(n, *[k.ctypes.data_as(C.c_void_p) for k in keep], *[o.ctypes.data_as(C.c_void_p) for o in outs])
+    for got, want in zip(outs[:5], (op, s, q, raw_op.grad, raw_s.grad)):
+        w = want.detach().numpy().reshape(-1)
+        assert np.all(np.abs(got - w) <= 2e-6 * np.maximum(np.abs(w), 1.0)), np.abs(got - w).max()
+    # the normalize derivative cancels (g - q (q.g)): the error scales with |g| / |r| of the row, not with the result
+    w = raw_q.grad.numpy()
+    scale = (g_q.norm(dim=1) / raw_q.detach().norm(dim=1).clamp_min(1e-12)).numpy()[:, None]
+    assert np.all(np.abs(outs[5].reshape(n, 4) - w) <= 4e-6 * scale), (np.abs(outs[5].reshape(n, 4) - w) / scale).max()

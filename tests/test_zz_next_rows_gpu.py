@@ -193,3 +193,116 @@ def test_dist_cuda2_one_million_points_against_a_sampled_exact_search():
     d, _ = cKDTree(p64).query(p64[idx], k=4)
     want = (d[:, 1:] ** 2).mean(axis=1)
     assert np.all(np.abs(got[idx] - want) <= 1e-5 * np.maximum(want, 1e-12) + 1e-12)
+
+
+# ------------------------------------------------------------------------------------------------ raw-parameter path (row 1)
+def _raw_model(P, seed, W=160, H=96, sh_degree=3, M=16):
+    from helpers import S
+    cam = S.look_at_camera(W, H, eye=(0.2, -0.1, -0.4), target=(0.0, 0.0, 5.0))
+    scene = S.make_scene(P, cam, sh_degree=sh_degree, M=M, seed=seed, s0_pix=3.0)
+    t = lambda a: torch.tensor(a, device="cuda")
+    g = torch.Generator().manual_seed(seed)
+    raw = dict(xyz=t(scene["means3D"]), f_dc=t(scene["shs"][:, :1, :].copy()), f_rest=t(scene["shs"][:, 1:, :].copy()),
+               opacity=torch.logit(t(scene["opacities"]).clamp(1e-4, 1 - 1e-4)), scaling=torch.log(t(scene["scales"])),
+               rotation=t(scene["rotations"]) * (0.2 + 3.0 * torch.rand(P, 1, generator=g).cuda()))      # NOT unit length
+    return cam, {k: v.contiguous().requires_grad_(True) for k, v in raw.items()}
+
+
+def _settings(mod, cam, sh_degree):
+    t = lambda a: torch.tensor(np.asarray(a), dtype=torch.float32, device="cuda")
+    return mod.GaussianRasterizationSettings(image_height=cam["H"], image_width=cam["W"], tanfovx=cam["tanfovx"], tanfovy=cam["tanfovy"],
+                                             bg=t([0.1, 0.2, 0.3]), scale_modifier=1.0, viewmatrix=t(cam["viewmatrix"]),
+                                             projmatrix=t(cam["projmatrix"]), sh_degree=sh_degree, campos=t(cam["campos"]),
+                                             prefiltered=False, debug=False)
+
+
+@pytest.mark.parametrize("P,deg,M", [(5000, 3, 16), (1, 3, 16), (777, 1, 16), (300, 0, 16), (2000, 2, 9), (900, 0, 1), (129, 1, 4)])
+def test_raw_parameter_path_equals_torch_activations_plus_the_rasterizer(P, deg, M):
+    """forward_raw(raw tensors) against forward(sigmoid / exp / normalize / cat of the same tensors) through torch autograd.
+    Bars: radii equal (at most 2 Gaussians may sit on a rounding boundary of the quaternion norm), image <= 1e-5 max-abs,
+    every raw-parameter gradient <= 1e-4 relative L2 (north_star's bars for the rasterizer itself)."""
+    import diff_gaussian_rasterization as mod
+    from helpers import rel_l2
+    cam, raw = _raw_model(P, seed=P + deg, sh_degree=deg, M=M)
+    rast = mod.GaussianRasterizer(_settings(mod, cam, deg))
+    w = torch.rand(3, cam["H"], cam["W"], device="cuda") * 2 - 1
+
+    def run(fused):
+        for v in raw.values():
+            v.grad = None
+        m2d = torch.zeros(P, 3, device="cuda", requires_grad=True)
+        if fused:
+            img, radii = rast.forward_raw(raw["xyz"], m2d, raw["f_dc"], raw["f_rest"], raw["opacity"], raw["scaling"], raw["rotation"])
+        else:
+            img, radii = rast(means3D=raw["xyz"], means2D=m2d, shs=torch.cat((raw["f_dc"], raw["f_rest"]), dim=1),
+                              opacities=torch.sigmoid(raw["opacity"]), scales=torch.exp(raw["scaling"]),
+                              rotations=torch.nn.functional.normalize(raw["rotation"]))
+        (img * w).sum().backward()
+        grads = {k: (v.grad.detach().clone() if v.grad is not None else torch.zeros_like(v)) for k, v in raw.items()}
+        grads["means2D"] = m2d.grad.detach().clone()
+        return img.detach(), radii, grads
+    img_f, rad_f, g_f = run(True)
+    img_u, rad_u, g_u = run(False)
+    assert int((rad_f != rad_u).sum()) <= 2
+    assert float((img_f - img_u).abs().max()) <= 1e-5
+    for k in g_u:
+        assert g_f[k].shape == g_u[k].shape
+        if g_u[k].numel() == 0:
+            continue
+        if float(g_u[k].abs().max()) == 0.0:
+            assert float(g_f[k].abs().max()) == 0.0, k
+        else:
+            assert rel_l2(g_f[k].cpu().numpy(), g_u[k].cpu().numpy()) <= 1e-4, k
+
+
+def test_fused_render_is_a_drop_in_for_the_reference_render():
+    import gsr_render
+    from helpers import S
+    P = 3000
+    cam, raw = _raw_model(P, seed=4)
+
+    class PC:          # the attributes of GaussianModel that render() touches (scene/gaussian_model.py:44-138)
+        active_sh_degree = 3
+        max_sh_degree = 3
+        _xyz, _features_dc, _features_rest = raw["xyz"], raw["f_dc"], raw["f_rest"]
+        _opacity, _scaling, _rotation = raw["opacity"], raw["scaling"], raw["rotation"]
+        scaling_activation, opacity_activation, rotation_activation = torch.exp, torch.sigmoid, torch.nn.functional.normalize
+        get_xyz = property(lambda s: s._xyz)
+        get_scaling = property(lambda s: s.scaling_activation(s._scaling))
+        get_rotation = property(lambda s: s.rotation_activation(s._rotation))
+        get_opacity = property(lambda s: s.opacity_activation(s._opacity))
+        get_features = property(lambda s: torch.cat((s._features_dc, s._features_rest), dim=1))
+
+    class Pipe:
+        convert_SHs_python = False
+        compute_cov3D_python = False
+        debug = False
+
+    class View:
+        FoVx = 2 * np.arctan(cam["tanfovx"]); FoVy = 2 * np.arctan(cam["tanfovy"])
+        image_height, image_width = cam["H"], cam["W"]
+        world_view_transform = torch.tensor(cam["viewmatrix"], device="cuda")
+        full_proj_transform = torch.tensor(cam["projmatrix"], device="cuda")
+        camera_center = torch.tensor(cam["campos"], device="cuda")
+
+    bg = torch.tensor([0.0, 0.0, 0.0], device="cuda")
+    pc = PC()
+    fused = gsr_render.render(View, pc, Pipe, bg)
+    assert set(fused) == {"render", "viewspace_points", "visibility_filter", "radii"}
+    fused["render"].sum().backward()
+    vs_grad = fused["viewspace_points"].grad.clone()
+    g_fused = {k: v.grad.clone() for k, v in raw.items()}
+    for v in raw.values():
+        v.grad = None
+    pc.scaling_activation = lambda x: torch.exp(x)            # not the default object: render() takes the reference's route
+    plain = gsr_render.render(View, pc, Pipe, bg)
+    plain["render"].sum().backward()
+    assert float((fused["render"] - plain["render"]).abs().max()) <= 1e-5
+    assert int((fused["radii"] != plain["radii"]).sum()) <= 2
+    assert torch.equal(fused["visibility_filter"], fused["radii"] > 0)
+    assert float((vs_grad - plain["viewspace_points"].grad).norm() / plain["viewspace_points"].grad.norm()) <= 1e-4
+    for k, v in raw.items():
+        assert float((g_fused[k] - v.grad).norm() / v.grad.norm().clamp_min(1e-30)) <= 1e-4, k
+    Pipe.convert_SHs_python = True                             # the python SH route (gsr_sh.eval_sh) gives the same picture
+    py_sh = gsr_render.render(View, pc, Pipe, bg)
+    assert float((py_sh["render"] - plain["render"]).abs().max()) <= 2e-5
