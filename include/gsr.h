@@ -239,8 +239,8 @@ int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, doub
  * Replaces distCUDA2 of the reference's simple-knn extension (submodules/simple-knn/spatial.cu:15-26, SimpleKNN::knn,
  * simple_knn.cu:185-221), used by GaussianModel.create_from_pcd to initialise the scales (scene/gaussian_model.py:207).
  * mean_dist2[i] = (d0 + d1 + d2) / 3 with d0 <= d1 <= d2 the three smallest squared distances from point i to the
- * other points (other = different index: coincident points count with distance 0); fewer than 4 points give +inf,
- * as the reference's FLT_MAX initialisation does.  points is (P,3) float32, scratch holds gsr_knn_scratch_bytes(P)
+ * other points (other = different index: coincident points count with distance 0); with fewer than 4 points the missing
+ * neighbours keep the reference's FLT_MAX placeholders (simple_knn.cu:159): +inf for 1 or 2 points, about FLT_MAX/3 for 3.  points is (P,3) float32, scratch holds gsr_knn_scratch_bytes(P)
  * bytes (256-byte aligned) and is free again when the call's work on the stream is done.  No host synchronisation. */
 size_t gsr_knn_scratch_bytes(int P);
 int gsr_knn_mean_dist2(int P, const float* points, float* mean_dist2, char* scratch, void* cuda_stream);
