@@ -406,7 +406,7 @@ template <int MINB, bool PACK, bool RAW, bool SPLIT>
 __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(PreprocessBwdArgs a, int S /* smem row stride, floats */) {
     __shared__ float s_cam[36];
     __shared__ uint8_t s_vis[PB];
-    extern __shared__ __align__(16) float s_dyn[];     // SH rows (PB x S), later re-used for the 27 other outputs
+    GSR_DYN_SMEM(s_dyn);                               // SH rows (PB x S), later re-used for the 27 other outputs
     float* s_sh = s_dyn;
     float* s_out = s_dyn;
     load_camera(a, s_cam);
@@ -428,8 +428,7 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
     if (SPLIT) {
         // rows [dc(3) | rest]: only the rest part is read by the backward (the DC coefficient has no direction derivative)
         stage_rest_rows<PB>(s_sh, S, a.f_rest + (size_t)row0 * (L - 3), nrows, L - 3, Kf - 3, s_vis, t);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        cp_async_commit_wait_all();
         __syncthreads();
     } else if (has_sh) {
         const float4* src = reinterpret_cast<const float4*>(a.shs + (size_t)row0 * L);
@@ -440,12 +439,11 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
         const uint32_t sh_base = smem_addr(s_sh);
         for (int e4 = t; e4 < n4; e4 += PB) {
             if (s_vis[row] && col < Kf4)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(sh_base + 4u * (uint32_t)(row * S + col)), "l"(src + e4) : "memory");
+                cp_async16(sh_base + 4u * (uint32_t)(row * S + col), src + e4);
             row += qstep; col += rstep;
             if (col >= L) { col -= L; row++; }
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        cp_async_commit_wait_all();
         __syncthreads();
     }
     BwdOut o;
@@ -507,6 +505,7 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
     }
 }
 
+#ifndef GSR_EMU   // defined only by the host-compiled kernel check in tests/, which brings its own launcher
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
     const int L = 3 * a.M;
@@ -547,6 +546,8 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     for (int c = nchunk - 1; a.chunk_events && c < a.n_chunk_events; c++) cudaEventRecord((cudaEvent_t)a.chunk_events[c], st);
 }
 
+#endif
+
 }  // namespace gsr
 
 // ------------------------------------------------------------------------------------------------
@@ -577,7 +578,7 @@ template <int DEG>
 __global__ void __launch_bounds__(MV) multiview_sh_grad_kernel(MultiviewShArgs a, int S) {
     constexpr int K = (DEG + 1) * (DEG + 1);
     constexpr int NF = 3 * K, NV = (NF + 3) / 4;
-    extern __shared__ __align__(16) float s_mv[];        // [n_views][MV*3] colour gradients, then MV rows of S floats
+    GSR_DYN_SMEM(s_mv);                                  // [n_views][MV*3] colour gradients, then MV rows of S floats
     float* s_rgb = s_mv;
     float* s_rows = s_mv + a.n_views * MV * 3;
     __shared__ float s_campos[16 * 4];
@@ -695,6 +696,7 @@ __global__ void __launch_bounds__(256) unpack_small_kernel(int begin, int end, c
     for (int i = threadIdx.x; i < nrows * 4; i += 256) drot[(size_t)row0 * 4 + i] = s[(i >> 2) * 14 + 10 + (i & 3)];
 }
 
+#ifndef GSR_EMU
 void launch_unpack_small(int begin, int end, const float* pack, float* dmean3D, float* dmean2D, float* dop, float* dscale,
                          float* drot, cudaStream_t st) {
     if (end <= begin) return;
@@ -735,5 +737,7 @@ void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st) {
         count_launch(1);
     }
 }
+
+#endif
 
 }  // namespace gsr

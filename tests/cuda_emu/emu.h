@@ -17,6 +17,9 @@
 #include <mutex>
 #include <thread>
 #include <vector>
+#include <cstdio>
+#include <cstdlib>
+#include <sys/mman.h>
 
 #undef __shared__
 #define __shared__ static           // blocks run one at a time, so one static instance == the block's shared memory
@@ -58,6 +61,17 @@ struct BlockCtx {
 extern BlockCtx g_ctx;
 extern thread_local int t_lane, t_warp;
 
+// Dynamic shared memory of the running block: one 96 KiB mapping BELOW 4 GiB, because the kernels address it through
+// 32-bit shared addresses (csrc/gsr_smem.cuh: smem_addr / lds128 / sts128).
+inline float* dyn_smem() {
+    static float* p = [] {
+        void* m = mmap(nullptr, 96 * 1024, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_32BIT, -1, 0);
+        if (m == MAP_FAILED) { std::perror("emu: mmap(MAP_32BIT)"); std::abort(); }
+        return static_cast<float*>(m);
+    }();
+    return p;
+}
+
 template <typename F> void launch(dim3 grid, dim3 block, F body);
 
 }  // namespace emu
@@ -91,6 +105,14 @@ inline unsigned __ballot_sync(unsigned, bool pred) {
     c.warp[emu::t_warp].wait();
     return r;
 }
+inline unsigned __reduce_add_sync(unsigned, unsigned v) {
+    unsigned s = v;
+    for (int o = 16; o >= 1; o >>= 1) s += emu_exchange(s, emu::t_lane ^ o);
+    return s;
+}
+inline unsigned atomicAdd(unsigned* p, unsigned v) { return std::atomic_ref<unsigned>(*p).fetch_add(v); }
+inline void __trap() { std::abort(); }
+inline float __frcp_rn(float a) { volatile float r = 1.0f / a; return r; }
 inline int __popc(unsigned x) { return __builtin_popcount(x); }
 template <typename T> inline T __ldg(const T* p) { return *p; }
 inline int __float_as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }

@@ -17,6 +17,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 EMU_DIR = os.path.join(HERE, "cuda_emu")
 SO = os.path.join(EMU_DIR, "libemu_next.so")
 SO_FUSED = os.path.join(EMU_DIR, "libemu_fused.so")
+SO_PRE = os.path.join(EMU_DIR, "libemu_preprocess.so")
+GOLDEN = os.path.join(HERE, "golden")
 CSRC = os.path.join(os.path.dirname(HERE), "gaussian-splatting_cc-comments_b200", "csrc")
 
 
@@ -229,3 +231,172 @@ def test_activations_and_their_derivatives_match_torch(emu_fused):
     w = raw_q.grad.numpy()
     scale = (g_q.norm(dim=1) / raw_q.detach().norm(dim=1).clamp_min(1e-12)).numpy()[:, None]
     assert np.all(np.abs(outs[5].reshape(n, 4) - w) <= 4e-6 * scale), (np.abs(outs[5].reshape(n, 4) - w) / scale).max()
+
+
+# ------------------------------------------------------------------ the per-Gaussian kernels themselves, on the host
+@pytest.fixture(scope="module")
+def emu_pre():
+    deps = [os.path.join(EMU_DIR, "emu_preprocess.cpp"), os.path.join(EMU_DIR, "emu.h")] + [
+        os.path.join(CSRC, f) for f in ("gsr_preprocess.cu", "gsr_preprocess_bwd.cu", "gsr_fused_params.cuh", "gsr_math.cuh", "gsr_smem.cuh",
+                                        "gsr_internal.cuh")]
+    if not os.path.exists(SO_PRE) or any(os.path.getmtime(SO_PRE) < os.path.getmtime(d) for d in deps):
+        r = subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-fPIC", "-shared", "-ffp-contract=off", "-mfma", "-w",
+                            "-I/usr/local/cuda/include", deps[0], "-o", SO_PRE], capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-3000:]
+    return C.CDLL(SO_PRE)
+
+
+def _vp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _al(a):
+    """16-byte aligned float32 copy (the staged kernels are chosen on alignment, as on the device)."""
+    a = np.asarray(a, np.float32)
+    v = _aligned(max(1, a.size))[:a.size]
+    v[:] = a.reshape(-1)
+    return v.reshape(a.shape)
+
+
+def _fwd(lib, z, D, smod=1.0, raw=0, split=False, scales=None, rots=None, opac=None, shs=None):
+    P, W, H = z["in_means3D"].shape[0], int(z["cam_W"]), int(z["cam_H"])
+    m = np.ascontiguousarray(z["in_means3D"])
+    sc = np.ascontiguousarray(z["in_scales"] if scales is None else scales, np.float32)
+    rt = _al(z["in_rotations"] if rots is None else rots)
+    op = np.ascontiguousarray(z["in_opacities"] if opac is None else opac, np.float32)
+    sh = _al(z["in_shs"] if shs is None else shs)
+    M = sh.shape[1]
+    dc, rest = _al(sh[:, :1, :]), _al(sh[:, 1:, :])
+    o = dict(radii=np.zeros(P, np.int32), packed=np.zeros((P, 12), np.float32), tt=np.zeros(P, np.uint32), cl=np.zeros(P, np.uint8),
+             dk=np.zeros(P, np.uint32))
+    tot = np.zeros(1, np.uint32)
+    view, proj, cp = (np.ascontiguousarray(z[k]) for k in ("cam_viewmatrix", "cam_projmatrix", "cam_campos"))
+    lib.emu_preprocess_fwd(P, D, M, _vp(m), _vp(sc), C.c_float(smod), _vp(rt), _vp(op), None if split else _vp(sh), _vp(dc) if split else None,
+                           _vp(rest) if split else None, _vp(view), _vp(proj), _vp(cp), W, H, C.c_float(float(z["cam_tanfovx"])),
+                           C.c_float(float(z["cam_tanfovy"])), raw, _vp(o["radii"]), _vp(o["packed"]), _vp(o["tt"]), _vp(o["cl"]), _vp(o["dk"]), _vp(tot))
+    o["total"] = int(tot[0])
+    return o
+
+
+@pytest.mark.parametrize("name,D,smod", [("ref_cuda_sh3_160x96", 3, 1.0), ("ref_cuda_sh1_mod_64x64", 1, 0.6)])
+def test_forward_kernel_source_reproduces_the_reference_builds_b200_fixture_on_the_host(emu_pre, name, D, smod):
+    """preprocess_fwd_kernel<false,false> -- the kernel source that runs on the GPU, compiled for the host -- against what
+    the reference's own CUDA build wrote on a B200: radii, tile counts, num_rendered, means2D, conic, opacity, colours,
+    clamp bits and depth keys, bit for bit (every rounding of this stage is pinned; it has no MUFU-dependent output)."""
+    z = np.load(os.path.join(GOLDEN, name + ".npz"))
+    o = _fwd(emu_pre, z, D, smod)
+    vis = z["out_radii"] > 0
+    assert np.array_equal(o["radii"], z["out_radii"]) and np.array_equal(o["tt"], z["out_tiles_touched"])
+    assert o["total"] == int(z["out_num_rendered"])
+    pk = o["packed"]
+    assert np.array_equal(pk[vis, 0:2], z["out_means2D"][vis])
+    assert np.array_equal(pk[vis][:, [2, 3, 4]], z["out_conic_opacity"][vis][:, :3]) and np.array_equal(pk[vis, 6], z["out_conic_opacity"][vis, 3])
+    assert np.array_equal(pk[vis, 7:10], z["out_rgb"][vis])
+    assert np.array_equal(o["dk"][vis].view(np.float32), z["out_depths"][vis])
+    bits = z["out_clamped"][:, 0].astype(np.uint8) | (z["out_clamped"][:, 1].astype(np.uint8) << 1) | (z["out_clamped"][:, 2].astype(np.uint8) << 2)
+    assert np.array_equal(o["cl"][vis], bits[vis])
+
+
+def _raw_inputs(emu_fused, z, seed=0):
+    rng = np.random.default_rng(seed)
+    P = z["in_means3D"].shape[0]
+    raw_s = np.ascontiguousarray(np.log(z["in_scales"]), np.float32)
+    raw_q = _al(z["in_rotations"] * rng.uniform(0.2, 3, size=(P, 1)))
+    raw_o = np.ascontiguousarray(np.log(z["in_opacities"] / (1 - z["in_opacities"])), np.float32).reshape(P)
+    return raw_o, raw_s, raw_q
+
+
+def _activate(emu_fused, raw_o, raw_s, raw_q, g_o=None, g_s=None, g_q=None):
+    P = raw_o.shape[0]
+    outs = [np.zeros(n, np.float32) for n in (P, 3 * P, 4 * P, P, 3 * P, 4 * P)]
+    g = [np.ascontiguousarray(np.zeros(n, np.float32) if x is None else x, np.float32).reshape(-1) for x, n in ((g_o, P), (g_s, 3 * P), (g_q, 4 * P))]
+    emu_fused.emu_activations(P, _vp(raw_o), _vp(raw_s), _vp(np.ascontiguousarray(raw_q)), _vp(g[0]), _vp(g[1]), _vp(g[2]), *[_vp(o) for o in outs])
+    return outs
+
+
+@pytest.mark.parametrize("M,D", [(16, 3), (16, 2), (16, 0), (9, 2), (4, 1), (1, 0)])
+def test_raw_parameter_forward_kernels_equal_the_reference_shaped_kernel(emu_pre, emu_fused, M, D):
+    """preprocess_fwd_kernel<RAW,SPLIT> on the raw tensors == <false,false> on the activated / concatenated ones, every
+    output bit for bit (activations evaluated by the same host functions on both sides)."""
+    z = np.load(os.path.join(GOLDEN, "ref_cuda_sh3_160x96.npz"))
+    P = z["in_means3D"].shape[0]
+    raw_o, raw_s, raw_q = _raw_inputs(emu_fused, z)
+    a = _activate(emu_fused, raw_o, raw_s, raw_q)
+    act_o, act_s, act_q = a[0].reshape(P, 1), a[1].reshape(P, 3), a[2].reshape(P, 4)
+    sh = z["in_shs"][:, :M, :]
+    base = _fwd(emu_pre, z, D, scales=act_s, rots=act_q, opac=act_o, shs=sh)
+    assert (base["radii"] > 0).sum() > 0.5 * P
+    for raw, split in ((1, False), (0, True), (1, True)):
+        o = _fwd(emu_pre, z, D, raw=raw, split=split, scales=raw_s if raw else act_s, rots=raw_q if raw else act_q,
+                 opac=raw_o.reshape(P, 1) if raw else act_o, shs=sh)
+        for k in ("radii", "packed", "tt", "cl", "dk"):
+            assert np.array_equal(o[k], base[k]), (raw, split, k)
+        assert o["total"] == base["total"]
+
+
+def _bwd(lib, z, fw, grad_acc, D, raw=0, split=False, scales=None, rots=None, shs=None, generic=0):
+    P, W, H = z["in_means3D"].shape[0], int(z["cam_W"]), int(z["cam_H"])
+    m = np.ascontiguousarray(z["in_means3D"])
+    sc, rt, sh = np.ascontiguousarray(scales, np.float32), _al(rots), _al(shs)
+    M = sh.shape[1]
+    dc, rest = _al(sh[:, :1, :]), _al(sh[:, 1:, :])
+    view, proj, cp = (np.ascontiguousarray(z[k]) for k in ("cam_viewmatrix", "cam_projmatrix", "cam_campos"))
+    widths = dict(mean2D=3, conic=4, opacity=1, color=3, mean3D=3, cov3D=6, sh=3 * M, scale=3, rot=4, dc=3, rest=3 * (M - 1))
+    out = {}
+    for k, w in widths.items():
+        out[k] = _aligned(max(1, P * w))
+        out[k][:] = np.nan                                   # every element must be written by the kernel
+    mode = lib.emu_preprocess_bwd(
+        P, D, M, _vp(m), _vp(fw["radii"]), None if split else _vp(sh), _vp(fw["cl"]), _vp(sc), _vp(rt), C.c_float(1.0), _vp(view), _vp(proj), _vp(cp),
+        W, H, C.c_float(float(z["cam_tanfovx"])), C.c_float(float(z["cam_tanfovy"])), _vp(grad_acc), _vp(fw["packed"]), raw,
+        _vp(dc) if split else None, _vp(rest) if split else None, generic, _vp(out["mean2D"]), _vp(out["conic"]), _vp(out["opacity"]),
+        _vp(out["color"]), _vp(out["mean3D"]), _vp(out["cov3D"]), None if split else _vp(out["sh"]), _vp(out["scale"]), _vp(out["rot"]),
+        _vp(out["dc"]) if split else None, _vp(out["rest"]) if split else None)
+    return mode, {k: v[:P * widths[k]] for k, v in out.items()}
+
+
+@pytest.mark.parametrize("M,D", [(16, 3), (16, 1), (16, 0), (9, 2), (4, 1), (1, 0)])
+def test_raw_parameter_backward_kernels_equal_the_reference_shaped_kernel_plus_the_chain_rule(emu_pre, emu_fused, M, D):
+    """preprocess_bwd_kernel_staged<8,false,RAW,SPLIT> against the reference-shaped kernel on the same accumulators:
+    geometry gradients identical, dL_dfeatures_dc / _rest == the two slices of dL_dsh, and the raw-parameter gradients ==
+    the activated ones pushed through the activation derivatives.  Bit for bit where both sides run the same staged
+    arithmetic; 1e-5 where the reference-shaped side is the generic kernel (M = 9, 1: another formulation of the SH term)."""
+    z = np.load(os.path.join(GOLDEN, "ref_cuda_sh3_160x96.npz"))
+    P = z["in_means3D"].shape[0]
+    rng = np.random.default_rng(M + D)
+    raw_o, raw_s, raw_q = _raw_inputs(emu_fused, z)
+    a = _activate(emu_fused, raw_o, raw_s, raw_q)
+    act_o, act_s, act_q = a[0].reshape(P, 1), a[1].reshape(P, 3), a[2].reshape(P, 4)
+    sh = z["in_shs"][:, :M, :]
+    fw = _fwd(emu_pre, z, D, scales=act_s, rots=act_q, opac=act_o, shs=sh)
+    ga = _al(rng.normal(size=(P, 12)) * (fw["radii"] > 0)[:, None])
+    mode_b, base = _bwd(emu_pre, z, fw, ga, D, scales=act_s, rots=act_q, shs=sh)
+    mode_f, fused = _bwd(emu_pre, z, fw, ga, D, raw=1, split=True, scales=raw_s, rots=raw_q, shs=sh)
+    assert mode_f == 3 and mode_b == (1 if (3 * M) % 4 == 0 else 2)
+    same_math = mode_b == 1
+
+    def eq(x, y, what):
+        assert not np.isnan(x).any(), what + ": not every element was written"
+        if same_math:
+            assert np.array_equal(x, y), what
+        else:
+            assert np.abs(x - y).max() <= 1e-5 * max(1.0, np.abs(y).max()), what
+    for k in ("mean2D", "conic", "color", "mean3D", "cov3D"):
+        eq(fused[k], base[k], k)
+    dsh = base["sh"].reshape(P, M, 3)
+    eq(fused["dc"], dsh[:, :1, :].reshape(-1), "dL_dfeatures_dc")
+    if M > 1:
+        eq(fused["rest"], dsh[:, 1:, :].reshape(-1), "dL_dfeatures_rest")
+    chain = _activate(emu_fused, raw_o, raw_s, raw_q, base["opacity"], base["scale"], base["rot"])
+    eq(fused["opacity"], chain[3], "dL_d(raw opacity)")
+    eq(fused["scale"], chain[4], "dL_d(raw scaling)")
+    eq(fused["rot"], chain[5], "dL_d(raw rotation)")
+    # culled Gaussians get exact zeros everywhere
+    culled = fw["radii"] <= 0
+    assert culled.any() and not fused["dc"].reshape(P, 3)[culled].any() and not fused["scale"].reshape(P, 3)[culled].any()
+    # the two options are independent
+    _, raw_only = _bwd(emu_pre, z, fw, ga, D, raw=1, split=False, scales=raw_s, rots=raw_q, shs=sh)
+    assert np.array_equal(raw_only["scale"], fused["scale"]) and np.array_equal(raw_only["rot"], fused["rot"])
+    eq(raw_only["sh"], base["sh"], "dL_dsh with raw activations only")
+    _, split_only = _bwd(emu_pre, z, fw, ga, D, raw=0, split=True, scales=act_s, rots=act_q, shs=sh)
+    assert np.array_equal(split_only["dc"], fused["dc"]) and np.array_equal(split_only["scale"], base["scale"])
