@@ -131,9 +131,12 @@ __device__ __forceinline__ void keep3(float d, float& b0, float& b1, float& b2) 
     b2 = fminf(b2, d);
 }
 
+// SELF: the staged box is the thread's own, entry `skip` is the thread's point (exclusion is by index, as the reference's `i == idx`)
+template <bool SELF>
 __device__ __forceinline__ void scan_staged(const float4* s_pts, int n, int skip, const float4& me, float& b0, float& b1, float& b2) {
+#pragma unroll 4
     for (int j = 0; j < n; j++) {
-        if (j == skip) continue;
+        if (SELF && j == skip) continue;
         const float4 c = s_pts[j];                                            // same address for the whole warp: broadcast
         // point - ref, as updateKBest; the clamp turns NaN / inf distances (non-finite input points) into "never inserted"
         keep3(fminf(sq3(c.x - me.x, c.y - me.y, c.z - me.z), FLT_MAX), b0, b1, b2);
@@ -178,7 +181,7 @@ __global__ void __launch_bounds__(KNN_BOX) knn_search_kernel(int P, const float4
         __syncthreads();                                                       // previous contents no longer read
         if (tid < cn) s_pts[tid] = sorted[cfirst + tid];
         __syncthreads();
-        if (valid) scan_staged(s_pts, cn, s == 0 ? tid : -1, me, b0, b1, b2);
+        if (valid) { if (s == 0) scan_staged<true>(s_pts, cn, tid, me, b0, b1, b2); else scan_staged<false>(s_pts, cn, -1, me, b0, b1, b2); }
     }
 
     // ---- the block's rejection radius: the largest third-best among its points ----
@@ -221,7 +224,7 @@ __global__ void __launch_bounds__(KNN_BOX) knn_search_kernel(int P, const float4
             if (tid < 2) s_box[tid] = boxes[2 * (size_t)cb + tid];
             __syncthreads();
             // the reference's test (simple_knn.cu:174-176): skip boxes farther than the current third-best
-            if (valid && !(box_point_d2(s_box[0], s_box[1], me) > b2)) scan_staged(s_pts, cn, -1, me, b0, b1, b2);
+            if (valid && !(box_point_d2(s_box[0], s_box[1], me) > b2)) scan_staged<false>(s_pts, cn, -1, me, b0, b1, b2);
         }
         __syncthreads();                                                       // before s_cand / s_warp_n are rewritten
     }
