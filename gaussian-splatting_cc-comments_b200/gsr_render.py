@@ -22,48 +22,52 @@ from diff_gaussian_rasterization import GaussianRasterizationSettings, GaussianR
 
 def _default_activations(pc):
     """The fused kernels hard-wire exp / sigmoid / normalize (GaussianModel.setup_functions, scene/gaussian_model.py:27-42)."""
-    return (getattr(pc, "scaling_activation", torch.exp) is torch.exp and getattr(pc, "opacity_activation", torch.sigmoid) is torch.sigmoid
-            and getattr(pc, "rotation_activation", torch.nn.functional.normalize) is torch.nn.functional.normalize)
+    wired = (("scaling_activation", torch.exp), ("opacity_activation", torch.sigmoid), ("rotation_activation", torch.nn.functional.normalize))
+    return all(getattr(pc, name, fn) is fn for name, fn in wired)
+
+
+def _settings_for(view, pc, pipe, bg_color, scaling_modifier):
+    return GaussianRasterizationSettings(
+        image_height=int(view.image_height), image_width=int(view.image_width),
+        tanfovx=math.tan(0.5 * view.FoVx), tanfovy=math.tan(0.5 * view.FoVy),
+        bg=bg_color, scale_modifier=scaling_modifier,
+        viewmatrix=view.world_view_transform, projmatrix=view.full_proj_transform,
+        sh_degree=pc.active_sh_degree, campos=view.camera_center, prefiltered=False, debug=pipe.debug)
+
+
+def _activated_inputs(view, pc, pipe, scaling_modifier, override_color):
+    """Keyword arguments of GaussianRasterizer.forward for the pipeline options the fused path does not cover
+    (gaussian_renderer/__init__.py:69-101): python-side covariance, python-side SH evaluation, a colour override."""
+    kw = {"opacities": pc.get_opacity}
+    if pipe.compute_cov3D_python:
+        kw["cov3D_precomp"] = pc.get_covariance(scaling_modifier)
+    else:
+        kw["scales"], kw["rotations"] = pc.get_scaling, pc.get_rotation
+    if override_color is not None:
+        kw["colors_precomp"] = override_color
+    elif pipe.convert_SHs_python:
+        from gsr_sh import eval_sh
+        coeffs = pc.get_features.transpose(1, 2).view(-1, 3, (pc.max_sh_degree + 1) ** 2)
+        towards = pc.get_xyz - view.camera_center.repeat(pc.get_features.shape[0], 1)
+        towards = towards / towards.norm(dim=1, keepdim=True)
+        kw["colors_precomp"] = torch.clamp_min(eval_sh(pc.active_sh_degree, coeffs, towards) + 0.5, 0.0)
+    else:
+        kw["shs"] = pc.get_features
+    return kw
 
 
 def render(viewpoint_camera, pc, pipe, bg_color, scaling_modifier=1.0, override_color=None):
-    screenspace_points = torch.zeros_like(pc.get_xyz, dtype=pc.get_xyz.dtype, requires_grad=True, device=pc.get_xyz.device) + 0
+    xyz = pc.get_xyz
+    # the tensor whose .grad carries the screen-space gradient the densification statistics read (train.py:157-158)
+    viewspace = torch.zeros_like(xyz, dtype=xyz.dtype, requires_grad=True, device=xyz.device) + 0
     try:
-        screenspace_points.retain_grad()
+        viewspace.retain_grad()
     except Exception:
         pass
-    tanfovx = math.tan(viewpoint_camera.FoVx * 0.5)
-    tanfovy = math.tan(viewpoint_camera.FoVy * 0.5)
-    raster_settings = GaussianRasterizationSettings(
-        image_height=int(viewpoint_camera.image_height), image_width=int(viewpoint_camera.image_width), tanfovx=tanfovx, tanfovy=tanfovy,
-        bg=bg_color, scale_modifier=scaling_modifier, viewmatrix=viewpoint_camera.world_view_transform,
-        projmatrix=viewpoint_camera.full_proj_transform, sh_degree=pc.active_sh_degree, campos=viewpoint_camera.camera_center,
-        prefiltered=False, debug=pipe.debug)
-    rasterizer = GaussianRasterizer(raster_settings=raster_settings)
-    means3D = pc.get_xyz
-    means2D = screenspace_points
+    rasterizer = GaussianRasterizer(raster_settings=_settings_for(viewpoint_camera, pc, pipe, bg_color, scaling_modifier))
     fused = (override_color is None and not pipe.convert_SHs_python and not pipe.compute_cov3D_python and _default_activations(pc))
     if fused:
-        rendered_image, radii = rasterizer.forward_raw(means3D, means2D, pc._features_dc, pc._features_rest, pc._opacity, pc._scaling,
-                                                       pc._rotation)
+        image, radii = rasterizer.forward_raw(xyz, viewspace, pc._features_dc, pc._features_rest, pc._opacity, pc._scaling, pc._rotation)
     else:
-        scales = rotations = cov3D_precomp = None
-        if pipe.compute_cov3D_python:
-            cov3D_precomp = pc.get_covariance(scaling_modifier)
-        else:
-            scales, rotations = pc.get_scaling, pc.get_rotation
-        shs = colors_precomp = None
-        if override_color is None:
-            if pipe.convert_SHs_python:
-                from gsr_sh import eval_sh
-                shs_view = pc.get_features.transpose(1, 2).view(-1, 3, (pc.max_sh_degree + 1) ** 2)
-                dir_pp = pc.get_xyz - viewpoint_camera.camera_center.repeat(pc.get_features.shape[0], 1)
-                dir_pp_normalized = dir_pp / dir_pp.norm(dim=1, keepdim=True)
-                colors_precomp = torch.clamp_min(eval_sh(pc.active_sh_degree, shs_view, dir_pp_normalized) + 0.5, 0.0)
-            else:
-                shs = pc.get_features
-        else:
-            colors_precomp = override_color
-        rendered_image, radii = rasterizer(means3D=means3D, means2D=means2D, shs=shs, colors_precomp=colors_precomp,
-                                           opacities=pc.get_opacity, scales=scales, rotations=rotations, cov3D_precomp=cov3D_precomp)
-    return {"render": rendered_image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii}
+        image, radii = rasterizer(means3D=xyz, means2D=viewspace, **_activated_inputs(viewpoint_camera, pc, pipe, scaling_modifier, override_color))
+    return {"render": image, "viewspace_points": viewspace, "visibility_filter": radii > 0, "radii": radii}
