@@ -77,6 +77,15 @@ def test_knn_kernels_match_the_oracle_bit_for_bit(emu, name, pts):
     assert np.array_equal(got, want), "%s: %d of %d values differ" % (name, int((got != want).sum()), got.size)
 
 
+@pytest.mark.skipif(os.environ.get("GSR_SLOW") != "1", reason="2 minutes of host emulation: set GSR_SLOW=1 (ran green when it was written)")
+def test_knn_more_than_256_boxes_walks_the_candidate_list_in_rounds(emu):
+    """66 000 points = 258 boxes: the box-to-box pruning loop of knn_search_kernel takes a second round of 256 candidates."""
+    rng = np.random.default_rng(5)
+    P = 66000
+    pts = np.concatenate([rng.normal(size=(P // 2, 3)) * 0.05, rng.uniform(-20, 20, size=(P - P // 2, 3))]).astype(np.float32)
+    assert np.array_equal(_knn(emu, pts), O.knn_mean_dist2(pts))
+
+
 def test_knn_non_finite_points_are_never_neighbours(emu):
     rng = np.random.default_rng(3)
     pts = rng.normal(size=(600, 3)).astype(np.float32)
