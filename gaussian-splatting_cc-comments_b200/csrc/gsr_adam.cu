@@ -113,7 +113,6 @@ __global__ void __launch_bounds__(ADAM_THREADS, 4) adam_kernel(const __grid_cons
 
 size_t adam_blocks(size_t n) { return (n + ADAM_TILE - 1) / ADAM_TILE; }
 
-#ifndef GSR_EMU   // defined only by the host-compiled kernel check in tests/, which brings its own launcher
 void launch_adam(const AdamLaunch& L, unsigned total_blocks, bool vec, cudaStream_t st) {
     if (total_blocks == 0) return;
     const bool masked = L.visible != nullptr;
@@ -126,6 +125,5 @@ void launch_adam(const AdamLaunch& L, unsigned total_blocks, bool vec, cudaStrea
     }
     count_launch(1);
 }
-#endif
 
 }  // namespace gsr

@@ -246,7 +246,6 @@ KnnState KnnState::carve(char* base, size_t P) {
     return s;
 }
 
-#ifndef GSR_EMU   // defined only by the host-compiled kernel check in tests/, which brings its own launcher
 void launch_knn(int P, const float* points, float* mean_d2, const KnnState& s, cudaStream_t st) {
     if (P <= 0) return;
     cudaMemsetAsync(s.bounds, 0, 8 * sizeof(int), st);
@@ -261,6 +260,5 @@ void launch_knn(int P, const float* points, float* mean_d2, const KnnState& s, c
     knn_search_kernel<<<nb, KNN_BOX, 0, st>>>(P, s.sorted, s.boxes, (int)nb, mean_d2);
     count_launch(2);
 }
-#endif
 
 }  // namespace gsr

@@ -216,7 +216,6 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
     }
 }
 
-#ifndef GSR_EMU   // defined only by the host-compiled kernel check in tests/, which brings its own launcher
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
     const unsigned nb = (unsigned)((a.P + 255) / 256);
@@ -227,7 +226,6 @@ void launch_preprocess(const PreprocessArgs& a, cudaStream_t st) {
     else preprocess_fwd_kernel<true, true><<<nb, 256, 0, st>>>(a);
     count_launch(1);
 }
-#endif
 
 // rasterizer_impl.cu:56-69 (checkFrustum) -> present[idx] = p_view.z > 0.2 (auxiliary.h:165)
 __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* __restrict__ means,
@@ -240,12 +238,10 @@ __global__ void __launch_bounds__(256) mark_visible_kernel(int P, const float* _
     present[idx] = !(depth <= 0.2f);
 }
 
-#ifndef GSR_EMU
 void launch_mark_visible(int P, const float* means, const float* view, unsigned char* present, cudaStream_t st) {
     if (P <= 0) return;
     mark_visible_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, means, view, present);
     count_launch(1);
 }
-#endif
 
 }  // namespace gsr

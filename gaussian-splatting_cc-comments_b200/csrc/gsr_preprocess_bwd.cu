@@ -505,7 +505,6 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
     }
 }
 
-#ifndef GSR_EMU   // defined only by the host-compiled kernel check in tests/, which brings its own launcher
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     if (a.P <= 0) return;
     const int L = 3 * a.M;
@@ -545,8 +544,6 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
     }
     for (int c = nchunk - 1; a.chunk_events && c < a.n_chunk_events; c++) cudaEventRecord((cudaEvent_t)a.chunk_events[c], st);
 }
-
-#endif
 
 }  // namespace gsr
 
@@ -696,7 +693,6 @@ __global__ void __launch_bounds__(256) unpack_small_kernel(int begin, int end, c
     for (int i = threadIdx.x; i < nrows * 4; i += 256) drot[(size_t)row0 * 4 + i] = s[(i >> 2) * 14 + 10 + (i & 3)];
 }
 
-#ifndef GSR_EMU
 void launch_unpack_small(int begin, int end, const float* pack, float* dmean3D, float* dmean2D, float* dop, float* dscale,
                          float* drot, cudaStream_t st) {
     if (end <= begin) return;
@@ -737,7 +733,5 @@ void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st) {
         count_launch(1);
     }
 }
-
-#endif
 
 }  // namespace gsr

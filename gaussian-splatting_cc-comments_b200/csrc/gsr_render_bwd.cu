@@ -128,8 +128,7 @@ __global__ void __launch_bounds__(256, 5) render_bwd_kernel(const uint2* __restr
                 const bool c = (pos < last_contributor) && !(power > 0.0f) && !(power < b.y) && !(alpha0 < 1.0f / 255.0f);
                 const float alpha = c ? alpha0 : 0.0f;
                 const float G = c ? G0 : 0.0f;
-                float inv;
-                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(1.0f - alpha));
+                const float inv = rcp_approx_ftz(1.0f - alpha);
                 T = T * inv;
                 const float dchannel_dcolor = alpha * T;
                 ar0 = last_alpha * lc0 + (1.f - last_alpha) * ar0;

@@ -19,7 +19,6 @@
 #include <vector>
 #include <cstdio>
 #include <cstdlib>
-#include <sys/mman.h>
 
 #undef __shared__
 #define __shared__ static           // blocks run one at a time, so one static instance == the block's shared memory
@@ -56,21 +55,20 @@ struct BlockCtx {
     Barrier block;
     Barrier warp[32];
     uint32_t xchg[32][32];         // per warp, per lane exchange slots
+    std::atomic<int> count{0};     // __syncthreads_count
 };
 
 extern BlockCtx g_ctx;
 extern thread_local int t_lane, t_warp;
 
-// Dynamic shared memory of the running block: one 96 KiB mapping BELOW 4 GiB, because the kernels address it through
-// 32-bit shared addresses (csrc/gsr_smem.cuh: smem_addr / lds128 / sts128).
-inline float* dyn_smem() {
-    static float* p = [] {
-        void* m = mmap(nullptr, 96 * 1024, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_32BIT, -1, 0);
-        if (m == MAP_FAILED) { std::perror("emu: mmap(MAP_32BIT)"); std::abort(); }
-        return static_cast<float*>(m);
-    }();
-    return p;
-}
+// "Shared memory" addressing: the kernels address shared memory through 32-bit shared addresses (csrc/gsr_smem.cuh:
+// smem_addr / lds* / sts*).  On the host a shared address is the signed 32-bit distance from an anchor object of the same
+// library to the byte -- static `__shared__` arrays and the dynamic window below all live in that library's data segment.
+extern char g_smem_anchor;
+inline uint32_t to_shared(const void* p) { return (uint32_t)(int32_t)(reinterpret_cast<const char*>(p) - &g_smem_anchor); }
+inline char* from_shared(uint32_t a) { return &g_smem_anchor + (int32_t)a; }
+extern float g_dyn_smem[24 * 1024];            // 96 KiB dynamic shared memory of the running block
+inline float* dyn_smem() { return g_dyn_smem; }
 
 template <typename F> void launch(dim3 grid, dim3 block, F body);
 
@@ -104,6 +102,53 @@ inline unsigned __ballot_sync(unsigned, bool pred) {
     for (int l = 0; l < 32; l++) r |= (c.xchg[emu::t_warp][l] & 1u) << l;
     c.warp[emu::t_warp].wait();
     return r;
+}
+inline void __syncwarp(unsigned = 0xffffffffu) { emu::g_ctx.warp[emu::t_warp].wait(); }
+inline int __syncthreads_count(int pred) {
+    emu::BlockCtx& c = emu::g_ctx;
+    if (pred) c.count.fetch_add(1);
+    c.block.wait();
+    const int r = c.count.load();
+    c.block.wait();
+    if (threadIdx.x == 0 && threadIdx.y == 0 && threadIdx.z == 0) c.count.store(0);
+    c.block.wait();
+    return r;
+}
+inline uint32_t __shfl_sync(unsigned, uint32_t v, int src) { return emu_exchange(v, src); }
+inline int __shfl_sync(unsigned, int v, int src) { return (int)emu_exchange((uint32_t)v, src); }
+inline float __shfl_sync(unsigned, float v, int src) { uint32_t b; std::memcpy(&b, &v, 4); b = emu_exchange(b, src); float r; std::memcpy(&r, &b, 4); return r; }
+inline uint32_t __shfl_xor_sync(unsigned, uint32_t v, int mask) { return emu_exchange(v, emu::t_lane ^ mask); }
+inline int __shfl_xor_sync(unsigned, int v, int mask) { return (int)emu_exchange((uint32_t)v, emu::t_lane ^ mask); }
+inline uint32_t __shfl_up_sync(unsigned, uint32_t v, unsigned d) { const uint32_t r = emu_exchange(v, emu::t_lane - (int)d); return emu::t_lane >= (int)d ? r : v; }
+inline int __shfl_up_sync(unsigned, int v, unsigned d) { return (int)__shfl_up_sync(0xffffffffu, (uint32_t)v, d); }
+inline double __shfl_xor_sync(unsigned, double v, int mask) {      // two 32-bit halves, as the hardware does it
+    uint64_t b; std::memcpy(&b, &v, 8);
+    const uint32_t lo = emu_exchange((uint32_t)b, emu::t_lane ^ mask), hi = emu_exchange((uint32_t)(b >> 32), emu::t_lane ^ mask);
+    b = ((uint64_t)hi << 32) | lo;
+    double r; std::memcpy(&r, &b, 8);
+    return r;
+}
+inline int __all_sync(unsigned m, bool pred) { return __ballot_sync(m, pred) == 0xffffffffu; }
+inline int __any_sync(unsigned m, bool pred) { return __ballot_sync(m, pred) != 0u; }
+inline unsigned __reduce_or_sync(unsigned, unsigned v) { unsigned s = v; for (int o = 16; o >= 1; o >>= 1) s |= emu_exchange(s, emu::t_lane ^ o); return s; }
+inline unsigned __reduce_max_sync(unsigned, unsigned v) { unsigned s = v; for (int o = 16; o >= 1; o >>= 1) { const unsigned t = emu_exchange(s, emu::t_lane ^ o); s = t > s ? t : s; } return s; }
+inline int __reduce_max_sync(unsigned, int v) { int s = v; for (int o = 16; o >= 1; o >>= 1) { const int t = (int)emu_exchange((uint32_t)s, emu::t_lane ^ o); s = t > s ? t : s; } return s; }
+inline unsigned __match_any_sync(unsigned, uint32_t v) {
+    emu::BlockCtx& c = emu::g_ctx;
+    c.xchg[emu::t_warp][emu::t_lane] = v;
+    c.warp[emu::t_warp].wait();
+    unsigned r = 0;
+    for (int l = 0; l < 32; l++) r |= (unsigned)(c.xchg[emu::t_warp][l] == v) << l;
+    c.warp[emu::t_warp].wait();
+    return r;
+}
+inline int __ffs(int x) { return __builtin_ffs(x); }
+inline int __clz(int x) { return x == 0 ? 32 : __builtin_clz((unsigned)x); }
+inline unsigned __brev(unsigned x) { unsigned r = 0; for (int i = 0; i < 32; i++) r |= ((x >> i) & 1u) << (31 - i); return r; }
+inline float atomicAdd(float* p, float v) {
+    std::atomic_ref<float> a(*p); float old = a.load();
+    while (!a.compare_exchange_weak(old, old + v)) {}
+    return old;
 }
 inline unsigned __reduce_add_sync(unsigned, unsigned v) {
     unsigned s = v;
@@ -156,15 +201,19 @@ template <typename T> inline T max(T a, T b) { return a > b ? a : b; }
 
 namespace emu {
 template <typename F> void launch(dim3 grid, dim3 block, F body) {
-    const int nt = (int)block.x;
+    const int nt = (int)(block.x * block.y * block.z);
+    for (unsigned bz = 0; bz < grid.z; bz++)
+    for (unsigned by = 0; by < grid.y; by++)
     for (unsigned bx = 0; bx < grid.x; bx++) {
         g_ctx.block.reset(nt);
+        g_ctx.count = 0;
         for (int w = 0; w < (nt + 31) / 32; w++) g_ctx.warp[w].reset(min(32, nt - 32 * w));
         std::vector<std::thread> th;
         th.reserve(nt);
         for (int t = 0; t < nt; t++)
             th.emplace_back([&, t] {
-                threadIdx = {(unsigned)t, 0, 0}; blockIdx = {bx, 0, 0}; blockDim = block; gridDim = grid;
+                threadIdx = {(unsigned)t % block.x, ((unsigned)t / block.x) % block.y, (unsigned)t / (block.x * block.y)};
+                blockIdx = {bx, by, bz}; blockDim = block; gridDim = grid;
                 t_lane = t & 31; t_warp = t >> 5;
                 body();
                 g_ctx.warp[t_warp].leave();
@@ -174,3 +223,33 @@ template <typename F> void launch(dim3 grid, dim3 block, F body) {
     }
 }
 }  // namespace emu
+
+// every emulation library defines these once
+#define GSR_EMU_DEFINE_GLOBALS                                                                         \
+    namespace emu { BlockCtx g_ctx; thread_local int t_lane, t_warp; char g_smem_anchor; float g_dyn_smem[24 * 1024]; } \
+    thread_local uint3 threadIdx, blockIdx;                                                            \
+    thread_local dim3 blockDim, gridDim;
+
+// The handful of CUDA runtime calls the product's host code makes, on host memory (streams and events are no-ops: the
+// emulation is synchronous), and the launch counter of gsr_internal.cuh.  Defined once per emulation library.
+#define GSR_EMU_DEFINE_RUNTIME                                                                                                   \
+    namespace gsr { static unsigned long long g_emu_launches = 0; void count_launch(int n) { g_emu_launches += (unsigned long long)n; } } \
+    GSR_EMU_DEFINE_CUDART
+#define GSR_EMU_DEFINE_CUDART                                                                                                    \
+    extern "C" {                                                                                                                 \
+    cudaError_t cudaMemsetAsync(void* p, int v, size_t n, cudaStream_t) { std::memset(p, v, n); return cudaSuccess; }            \
+    cudaError_t cudaMemcpyAsync(void* d, const void* s, size_t n, cudaMemcpyKind, cudaStream_t) { std::memcpy(d, s, n); return cudaSuccess; } \
+    cudaError_t cudaGetLastError(void) { return cudaSuccess; }                                                                   \
+    cudaError_t cudaStreamSynchronize(cudaStream_t) { return cudaSuccess; }                                                      \
+    cudaError_t cudaGetDevice(int* d) { *d = 0; return cudaSuccess; }                                                            \
+    cudaError_t cudaStreamCreateWithFlags(cudaStream_t* s, unsigned) { *s = reinterpret_cast<cudaStream_t>(1); return cudaSuccess; } \
+    cudaError_t cudaEventCreateWithFlags(cudaEvent_t* e, unsigned) { *e = reinterpret_cast<cudaEvent_t>(1); return cudaSuccess; } \
+    cudaError_t cudaEventCreate(cudaEvent_t* e) { *e = reinterpret_cast<cudaEvent_t>(1); return cudaSuccess; }                   \
+    cudaError_t cudaHostAlloc(void** p, size_t n, unsigned) { *p = std::malloc(n); return *p ? cudaSuccess : cudaErrorMemoryAllocation; } \
+    cudaError_t cudaEventRecord(cudaEvent_t, cudaStream_t) { return cudaSuccess; }                                               \
+    cudaError_t cudaStreamWaitEvent(cudaStream_t, cudaEvent_t, unsigned) { return cudaSuccess; }                                 \
+    cudaError_t cudaEventSynchronize(cudaEvent_t) { return cudaSuccess; }                                                        \
+    cudaError_t cudaEventQuery(cudaEvent_t) { return cudaSuccess; }                                                              \
+    cudaError_t cudaEventElapsedTime(float* ms, cudaEvent_t, cudaEvent_t) { *ms = 0.f; return cudaSuccess; }                     \
+    const char* cudaGetErrorString(cudaError_t) { return "emulated CUDA runtime"; }                                              \
+    }

@@ -4,11 +4,9 @@
 #define GSR_EMU 1
 #include "emu.h"
 
-namespace emu { BlockCtx g_ctx; thread_local int t_lane, t_warp; }
-thread_local uint3 threadIdx, blockIdx;
-thread_local dim3 blockDim, gridDim;
+GSR_EMU_DEFINE_GLOBALS
 
-#include "../../gaussian-splatting_cc-comments_b200/csrc/gsr_fused_params.cuh"
+#include "gsr_fused_params.cuh"
 
 using namespace gsr;
 

@@ -3,14 +3,13 @@
 #define GSR_EMU 1
 #include "emu.h"
 
-namespace emu { BlockCtx g_ctx; thread_local int t_lane, t_warp; }
-thread_local uint3 threadIdx, blockIdx;
-thread_local dim3 blockDim, gridDim;
+GSR_EMU_DEFINE_GLOBALS
+GSR_EMU_DEFINE_RUNTIME      // count_launch + the few CUDA runtime calls the host code makes
 
-#include <algorithm>
 
-#include "../../gaussian-splatting_cc-comments_b200/csrc/gsr_adam.cu"
-#include "../../gaussian-splatting_cc-comments_b200/csrc/gsr_knn.cu"
+#include "_gen/gsr_adam.cpp"
+#include "_gen/gsr_binning.cpp"
+#include "_gen/gsr_knn.cpp"
 
 using namespace gsr;
 
@@ -48,25 +47,14 @@ int emu_adam_step(int n_groups, float** param, const float** grad, float** exp_a
     return vec ? 1 : 2;
 }
 
-// launch_knn (csrc/gsr_knn.cu) with the radix sort replaced by std::stable_sort (the sort kernels are covered on the GPU)
+// gsr_knn_mean_dist2 as csrc/gsr_api.cu runs it: the product's own launch_knn, radix sort included
 int emu_knn_mean_dist2(int P, const float* points, float* mean_d2) {
     if (P <= 0) return 0;
     KnnState sizes = KnnState::carve(nullptr, (size_t)P);
     std::vector<char> raw(sizes.bytes + 256);
     char* base = raw.data() + (256 - ((uintptr_t)raw.data() & 255)) % 256;
-    KnnState s = KnnState::carve(base, (size_t)P);
-    std::memset(s.bounds, 0, 8 * sizeof(int));
-    const unsigned rb = (unsigned)min((size_t)4, ((size_t)P + 255) / 256);      // few blocks: exercises the grid stride
-    emu::launch(dim3(rb), dim3(256), [&] { knn_bounds_kernel(P, points, s.bounds); });
-    emu::launch(dim3((unsigned)(((size_t)P + 255) / 256)), dim3(256), [&] { knn_morton_kernel(P, points, s.bounds, s.keys[0], s.vals[0]); });
-    std::vector<uint32_t> order(P);
-    for (int i = 0; i < P; i++) order[i] = (uint32_t)i;
-    std::stable_sort(order.begin(), order.end(), [&](uint32_t a, uint32_t b) { return (s.keys[0][a] & 0x3FFFFFFFu) < (s.keys[0][b] & 0x3FFFFFFFu); });
-    for (int i = 0; i < P; i++) { s.keys[1][i] = s.keys[0][order[i]]; s.vals[1][i] = s.vals[0][order[i]]; }
-    const unsigned nb = (unsigned)knn_boxes((size_t)P);
-    emu::launch(dim3(nb), dim3(KNN_BOX), [&] { knn_gather_kernel(P, points, s.vals[1], s.sorted, s.boxes); });
-    emu::launch(dim3(nb), dim3(KNN_BOX), [&] { knn_search_kernel(P, s.sorted, s.boxes, (int)nb, mean_d2); });
-    return (int)nb;
+    launch_knn(P, points, mean_d2, KnnState::carve(base, (size_t)P), nullptr);
+    return (int)knn_boxes((size_t)P);
 }
 
 }  // extern "C"

@@ -6,12 +6,11 @@
 #define GSR_EMU 1
 #include "emu.h"
 
-namespace emu { BlockCtx g_ctx; thread_local int t_lane, t_warp; }
-thread_local uint3 threadIdx, blockIdx;
-thread_local dim3 blockDim, gridDim;
+GSR_EMU_DEFINE_GLOBALS
+GSR_EMU_DEFINE_RUNTIME      // count_launch + the few CUDA runtime calls the host code makes
 
-#include "../../gaussian-splatting_cc-comments_b200/csrc/gsr_preprocess.cu"
-#include "../../gaussian-splatting_cc-comments_b200/csrc/gsr_preprocess_bwd.cu"
+#include "_gen/gsr_preprocess.cpp"
+#include "_gen/gsr_preprocess_bwd.cpp"
 
 using namespace gsr;
 

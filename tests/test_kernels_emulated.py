@@ -15,22 +15,25 @@ from oracle import gs_next_oracle as O
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 EMU_DIR = os.path.join(HERE, "cuda_emu")
-SO = os.path.join(EMU_DIR, "libemu_next.so")
-SO_FUSED = os.path.join(EMU_DIR, "libemu_fused.so")
-SO_PRE = os.path.join(EMU_DIR, "libemu_preprocess.so")
+SO_DIR = os.environ.get("GSR_EMU_SO_DIR", EMU_DIR)      # tools/emu_sanitize.sh points this at sanitizer builds
+SO = os.path.join(SO_DIR, "libemu_next.so")
+SO_FUSED = os.path.join(SO_DIR, "libemu_fused.so")
+SO_PRE = os.path.join(SO_DIR, "libemu_preprocess.so")
 GOLDEN = os.path.join(HERE, "golden")
 CSRC = os.path.join(os.path.dirname(HERE), "gaussian-splatting_cc-comments_b200", "csrc")
 
 
+def _build(name, so):
+    """Generated sources + g++ (tests/cuda_emu/build_emu.py); prebuilt sanitizer libraries are used as they are."""
+    import sys
+    sys.path.insert(0, EMU_DIR)
+    import build_emu
+    return build_emu.build(name) if so.startswith(EMU_DIR) else so
+
+
 @pytest.fixture(scope="module")
 def emu():
-    deps = [os.path.join(EMU_DIR, "emu_next.cpp"), os.path.join(EMU_DIR, "emu.h"), os.path.join(CSRC, "gsr_adam.cu"),
-            os.path.join(CSRC, "gsr_knn.cu"), os.path.join(CSRC, "gsr_internal.cuh")]
-    if not os.path.exists(SO) or any(os.path.getmtime(SO) < os.path.getmtime(d) for d in deps):
-        r = subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-fPIC", "-shared", "-ffp-contract=off", "-mfma", "-w",
-                            "-I/usr/local/cuda/include", deps[0], "-o", SO], capture_output=True, text=True)
-        assert r.returncode == 0, r.stderr[-3000:]
-    lib = C.CDLL(SO)
+    lib = C.CDLL(_build("emu_next", SO))
     lib.emu_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p]
     lib.emu_adam_step.argtypes = [C.c_int] + [C.c_void_p] * 8 + [C.c_double] * 3 + [C.c_void_p, C.c_int]
     return lib
@@ -38,13 +41,7 @@ def emu():
 
 @pytest.fixture(scope="module")
 def emu_fused():
-    deps = [os.path.join(EMU_DIR, "emu_fused.cpp"), os.path.join(EMU_DIR, "emu.h"), os.path.join(CSRC, "gsr_fused_params.cuh"),
-            os.path.join(CSRC, "gsr_math.cuh")]
-    if not os.path.exists(SO_FUSED) or any(os.path.getmtime(SO_FUSED) < os.path.getmtime(d) for d in deps):
-        r = subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-fPIC", "-shared", "-ffp-contract=off", "-mfma", "-w",
-                            "-I/usr/local/cuda/include", deps[0], "-o", SO_FUSED], capture_output=True, text=True)
-        assert r.returncode == 0, r.stderr[-3000:]
-    return C.CDLL(SO_FUSED)
+    return C.CDLL(_build("emu_fused", SO_FUSED))
 
 
 def _knn(lib, pts):
@@ -245,14 +242,7 @@ def test_activations_and_their_derivatives_match_torch(emu_fused):
 # ------------------------------------------------------------------ the per-Gaussian kernels themselves, on the host
 @pytest.fixture(scope="module")
 def emu_pre():
-    deps = [os.path.join(EMU_DIR, "emu_preprocess.cpp"), os.path.join(EMU_DIR, "emu.h")] + [
-        os.path.join(CSRC, f) for f in ("gsr_preprocess.cu", "gsr_preprocess_bwd.cu", "gsr_fused_params.cuh", "gsr_math.cuh", "gsr_smem.cuh",
-                                        "gsr_internal.cuh")]
-    if not os.path.exists(SO_PRE) or any(os.path.getmtime(SO_PRE) < os.path.getmtime(d) for d in deps):
-        r = subprocess.run(["g++", "-std=c++20", "-O1", "-pthread", "-fPIC", "-shared", "-ffp-contract=off", "-mfma", "-w",
-                            "-I/usr/local/cuda/include", deps[0], "-o", SO_PRE], capture_output=True, text=True)
-        assert r.returncode == 0, r.stderr[-3000:]
-    return C.CDLL(SO_PRE)
+    return C.CDLL(_build("emu_preprocess", SO_PRE))
 
 
 def _vp(a):

@@ -1,0 +1,27 @@
+# The host-emulated kernel and ABI tests (tests/test_kernels_emulated.py, tests/test_abi_emulated.py) under a sanitizer:
+#   bash tools/emu_sanitize.sh address   out-of-bounds reads / writes of the kernels on host arrays (numpy's buffers get
+#                                        red zones through the preloaded runtime) -- the host stand-in for memcheck
+#   bash tools/emu_sanitize.sh thread    data races between the emulated threads of a block, i.e. a missing
+#                                        __syncthreads() / __syncwarp() -- the host stand-in for racecheck
+# CPU only, several minutes.  Prints the pytest summary and the number of sanitizer reports (0 = clean).
+set -eu
+cd "$(dirname "$0")/.."
+KIND=${1:-address}
+D=/tmp/emu_$KIND; mkdir -p $D
+python - "$KIND" "$D" <<'PY'
+import sys
+sys.path.insert(0, "tests/cuda_emu")
+import build_emu
+kind, d = sys.argv[1], sys.argv[2]
+flags = ["-g", "-fsanitize=" + kind] + (["-fno-omit-frame-pointer"] if kind == "address" else [])
+for n in ("emu_next", "emu_fused", "emu_preprocess", "emu_abi"):
+    print(build_emu.build(n, extra_flags=flags, out="%s/lib%s.so" % (d, n)))
+PY
+if [ "$KIND" = address ]; then
+  export LD_PRELOAD=$(gcc -print-file-name=libasan.so) ASAN_OPTIONS=detect_leaks=0:halt_on_error=0
+else
+  export LD_PRELOAD=$(gcc -print-file-name=libtsan.so) TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 exitcode=0"
+fi
+GSR_EMU_SO_DIR=$D GSR_EMU_ABI_SO=$D/libemu_abi.so python -m pytest tests/test_kernels_emulated.py tests/test_abi_emulated.py -q -p no:cacheprovider > $D/run.log 2>&1 || true
+tail -3 $D/run.log
+echo "sanitizer reports: $(grep -c -E 'ERROR: AddressSanitizer|WARNING: ThreadSanitizer' $D/run.log || true)"
