@@ -220,3 +220,34 @@ def test_adam_and_knn_entry_points_on_the_host(abi):
     abi.gsr_knn_mean_dist2.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     assert abi.gsr_knn_mean_dist2(1500, _p(pts), _p(out), C.c_void_p(scratch), None) == 0, abi.gsr_last_error()
     assert np.array_equal(out, O.knn_mean_dist2(pts))
+
+
+def test_fused_l1_ssim_loss_entry_points_on_the_host(abi):
+    """Row 3 (GPU-verified in round 1) through the same host build: value, l1, ssim and dL/dimg against the float64
+    restatement of utils/loss_utils.py (tests/loss_ref.py), at the tolerances of tests/test_loss_gpu.py; the image
+    is not a multiple of the kernel's tile in either direction, so the halo / ragged-edge code runs."""
+    import torch
+    from loss_ref import loss_and_grad
+    rng = np.random.default_rng(7)
+    planes, H, W, lam = 3, 37, 53, 0.2
+    gt = _f32(rng.random((planes, H, W)))
+    img = _f32(np.clip(gt + rng.normal(size=gt.shape) * 0.1, 0, 1))
+    n = planes * H * W
+    abi.gsr_l1_ssim_scratch_floats.restype = C.c_size_t
+    abi.gsr_l1_ssim_scratch_floats.argtypes = [C.c_int, C.c_int, C.c_int]
+    scratch = np.zeros(abi.gsr_l1_ssim_scratch_floats(planes, H, W) + 64, np.float32)
+    dm = np.full(3 * n, np.nan, np.float32)
+    out3 = np.full(3, np.nan, np.float32)
+    abi.gsr_l1_ssim_forward.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p,
+                                        C.c_void_p, C.c_void_p]
+    assert abi.gsr_l1_ssim_forward(_p(img), _p(gt), planes, H, W, lam, _p(dm), _p(scratch), _p(out3), None) == 0, abi.gsr_last_error()
+    ref = loss_and_grad(torch.from_numpy(img), torch.from_numpy(gt), lam)
+    assert abs(out3[0] - ref["loss"]) < 2e-6 and abs(out3[1] - ref["l1"]) < 2e-6 and abs(out3[2] - ref["ssim"]) < 2e-6, (out3, ref)
+    assert np.isfinite(dm).all()
+    grad = np.full((planes, H, W), np.nan, np.float32)
+    abi.gsr_l1_ssim_backward.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
+                                         C.c_void_p, C.c_void_p, C.c_void_p]
+    assert abi.gsr_l1_ssim_backward(_p(img), _p(gt), _p(dm), planes, H, W, (1 - lam) / n, -lam / n, None, _p(grad), None) == 0, \
+        abi.gsr_last_error()
+    assert np.isfinite(grad).all()
+    assert _rel_l2(grad, ref["grad"]) <= 1e-4, _rel_l2(grad, ref["grad"])
