@@ -18,7 +18,7 @@ LIB = os.path.join(HERE, "libgsr_b200.so")
 EXT = os.path.join(HERE, "diff_gaussian_rasterization", "_C.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
-CU = ["gsr_api.cu", "gsr_preprocess.cu", "gsr_binning.cu", "gsr_render.cu", "gsr_render_bwd.cu", "gsr_preprocess_bwd.cu", "gsr_exchange.cu", "gsr_loss.cu", "gsr_adam.cu", "gsr_knn.cu"]
+CU = ["gsr_api.cu", "gsr_preprocess.cu", "gsr_binning.cu", "gsr_render.cu", "gsr_render_bwd.cu", "gsr_preprocess_bwd.cu", "gsr_exchange.cu", "gsr_loss.cu", "gsr_adam.cu", "gsr_knn.cu", "gsr_densify.cu"]
 
 
 def _newer(out, deps):

@@ -433,6 +433,94 @@ int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, doub
     return GSR_OK;
 }
 
+// ---- densification (train.py:153-158, scene/gaussian_model.py:558-602) ----
+int gsr_densify_stats(int P, const float* viewspace_grad, const int* radii, float* xyz_gradient_accum, float* denom,
+                      float* max_radii2D, void* cuda_stream) {
+    if (P < 0) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_stats: negative Gaussian count");
+    if (P == 0) return GSR_OK;
+    if (!viewspace_grad || !radii || !xyz_gradient_accum || !denom) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_stats: null pointer");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_densify_stats(P, viewspace_grad, radii, xyz_gradient_accum, denom, max_radii2D, st);
+    GSR_STAGE("densify stats", st, 0);
+    return GSR_OK;
+}
+
+static int densify_thresholds(const gsr_densify_params* p, DensifyThresholds& t) {
+    if (!p) return fail(GSR_ERR_INVALID_ARGUMENT, "densify: null params");
+    if (p->n_split_copies < 1 || p->n_split_copies > DENSIFY_MAX_COPIES)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "densify: n_split_copies must be in [1, " + std::to_string(DENSIFY_MAX_COPIES) + "]");
+    // Python evaluates percent_dense * extent, 0.1 * extent and 0.8 * N in double; torch rounds the scalar to the tensor's float32
+    t.max_grad = (float)p->max_grad;
+    t.dense_extent = (float)(p->percent_dense * p->extent);
+    t.big_extent = (float)(0.1 * p->extent);
+    t.min_opacity = (float)p->min_opacity;
+    t.inv_shrink = 1.0f / (float)(0.8 * p->n_split_copies);
+    t.use_screen = p->max_screen_size != 0.0;                        // `if max_screen_size:`
+    t.copies = p->n_split_copies;
+    return GSR_OK;
+}
+
+size_t gsr_densify_scratch_bytes(int P) { return P > 0 ? DensifyState::carve(nullptr, (size_t)P).bytes : 0; }
+
+int gsr_densify_classify(int P, const float* xyz_gradient_accum, const float* denom, const float* scaling_raw,
+                         const float* opacity_raw, const gsr_densify_params* params, unsigned char* flags, int* totals,
+                         char* scratch, void* cuda_stream) {
+    if (P < 0) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_classify: negative Gaussian count");
+    DensifyThresholds t;
+    if (int e = densify_thresholds(params, t)) return e;
+    if (!totals) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_classify: null totals");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    if (P == 0) { GSR_CUDA(cudaMemsetAsync(totals, 0, 5 * sizeof(int), st)); return GSR_OK; }
+    if (!xyz_gradient_accum || !denom || !scaling_raw || !opacity_raw || !flags || !scratch)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "densify_classify: null pointer");
+    if (((uintptr_t)scratch & 255) != 0) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_classify: scratch must be 256-byte aligned");
+    launch_densify_classify(P, xyz_gradient_accum, denom, scaling_raw, opacity_raw, t, flags, totals, DensifyState::carve(scratch, (size_t)P), st);
+    GSR_STAGE("densify classify", st, 0);
+    return GSR_OK;
+}
+
+int gsr_densify_apply(int P, const unsigned char* flags, const char* scratch, const int* totals_host,
+                      const gsr_densify_params* params, const float* samples, const gsr_densify_group* groups, int n_groups,
+                      int xyz_group, int scaling_group, int rotation_group, void* cuda_stream) {
+    if (P < 0) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: negative Gaussian count");
+    DensifyApply A;
+    if (int e = densify_thresholds(params, A.t)) return e;
+    if (P == 0) return GSR_OK;
+    if (!flags || !scratch || !totals_host || !groups) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: null pointer");
+    if (n_groups < 1 || n_groups > DENSIFY_MAX_GROUPS) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: 1 to 8 tensor groups");
+    const long long P_out = totals_host[0], n_split = totals_host[1], n_ok = totals_host[2], n_ck = totals_host[3], n_chk = totals_host[4];
+    if (n_ok < 0 || n_ck < 0 || n_chk < 0 || n_split < n_chk || n_ok + n_split > P || n_ck > P ||
+        P_out != n_ok + n_ck + (long long)A.t.copies * n_chk)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: totals are not the ones gsr_densify_classify wrote for this model");
+    if (P_out > 2147483647LL) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: result too large");
+    auto role_ok = [&](int gi, int w) { return gi >= 0 && gi < n_groups && groups[gi].row_width == w; };
+    if (!role_ok(xyz_group, 3) || !role_ok(scaling_group, 3) || !role_ok(rotation_group, 4) || xyz_group == scaling_group)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: xyz / scaling / rotation group indices or row widths are wrong");
+    if (n_split > 0 && !samples) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: samples needed for the split");
+    for (int i = 0; i < n_groups; i++) {
+        const gsr_densify_group& g = groups[i];
+        if (g.row_width < 1) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: row_width must be >= 1 in group " + std::to_string(i));
+        if (!g.param || (P_out > 0 && !g.param_out)) return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: null tensor in group " + std::to_string(i));
+        const bool has_state = g.exp_avg || g.exp_avg_sq;
+        if (has_state && (!g.exp_avg || !g.exp_avg_sq || (P_out > 0 && (!g.exp_avg_out || !g.exp_avg_sq_out))))
+            return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: moments must come in pairs, with outputs, in group " + std::to_string(i));
+        if (g.param_out == g.param || (has_state && (g.exp_avg_out == g.exp_avg || g.exp_avg_sq_out == g.exp_avg_sq)))
+            return fail(GSR_ERR_INVALID_ARGUMENT, "densify_apply: outputs must not alias the inputs (group " + std::to_string(i) + ")");
+        A.g[i] = DensifyGroupDev{g.param, g.exp_avg, g.exp_avg_sq, g.param_out, has_state ? g.exp_avg_out : nullptr,
+                                 has_state ? g.exp_avg_sq_out : nullptr, g.row_width};
+    }
+    for (int i = n_groups; i < DENSIFY_MAX_GROUPS; i++) A.g[i] = DensifyGroupDev{nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 1};
+    A.n_groups = n_groups; A.xyz_group = xyz_group; A.scaling_group = scaling_group; A.rotation_group = rotation_group;
+    A.P = P; A.n_split = (int)n_split; A.n_ok = (int)n_ok; A.n_ck = (int)n_ck; A.n_chk = (int)n_chk;
+    A.flags = flags;
+    A.block_offsets = DensifyState::carve(const_cast<char*>(scratch), (size_t)P).block_offsets;
+    A.samples = samples;
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_densify_apply(A, st);
+    GSR_STAGE("densify apply", st, 0);
+    return GSR_OK;
+}
+
 // ---- distCUDA2 of simple-knn ----
 size_t gsr_knn_scratch_bytes(int P) { return P > 0 ? KnnState::carve(nullptr, (size_t)P).bytes : 0; }
 

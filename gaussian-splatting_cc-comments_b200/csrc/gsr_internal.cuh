@@ -230,6 +230,39 @@ struct AdamLaunch {
 size_t adam_blocks(size_t n);
 void launch_adam(const AdamLaunch& L, unsigned total_blocks, bool vec, cudaStream_t st);
 
+// ---- densification: statistics, classify, apply (gsr_densify.cu) -----------------------------------------
+constexpr int DENSIFY_THREADS = 256;       // Gaussians per block in classify and apply (the ranks are per block)
+constexpr int DENSIFY_MAX_GROUPS = 8;
+constexpr int DENSIFY_MAX_COPIES = 8;
+struct DensifyThresholds {                 // the Python scalars of densify_and_prune, rounded to float32 as torch does
+    float max_grad, dense_extent, big_extent, min_opacity, inv_shrink;
+    int use_screen, copies;
+};
+struct DensifyState {
+    uint32_t* block_offsets;               // 4 x nblocks: per-block counts, then exclusive offsets (kept originals, kept
+                                           // clones, split parents, split parents with kept children)
+    size_t bytes;
+    static DensifyState carve(char* base, size_t P);
+};
+struct DensifyGroupDev {
+    const float* p; const float* m; const float* v;
+    float* po; float* mo; float* vo;
+    int w;
+};
+struct DensifyApply {
+    DensifyGroupDev g[DENSIFY_MAX_GROUPS];
+    int n_groups, xyz_group, scaling_group, rotation_group;
+    int P, n_split, n_ok, n_ck, n_chk;     // totals read back by the caller
+    const uint8_t* flags;
+    const uint32_t* block_offsets;
+    const float* samples;
+    DensifyThresholds t;
+};
+void launch_densify_stats(int P, const float* vs_grad, const int* radii, float* accum, float* denom, float* max_radii, cudaStream_t st);
+void launch_densify_classify(int P, const float* accum, const float* denom, const float* scaling, const float* opacity,
+                             const DensifyThresholds& t, uint8_t* flags, int* totals, const DensifyState& s, cudaStream_t st);
+void launch_densify_apply(const DensifyApply& a, cudaStream_t st);
+
 // ---- 3-nearest-neighbour mean squared distance (gsr_knn.cu) ------------------------------------------
 struct KnnState {
     uint32_t* keys[2];         // P each: Morton codes, ping-pong

@@ -235,6 +235,61 @@ typedef struct gsr_adam_group {
 int gsr_adam_step(const gsr_adam_group* groups, int n_groups, double beta1, double beta2, double eps,
                   const unsigned char* visible, void* cuda_stream);
 
+/* ---- Densification statistics, every iteration (train.py:153-158) ----
+ * Replaces, in one pass and without the host synchronisations of boolean-mask indexing,
+ *     max_radii2D[vis] = max(max_radii2D[vis], radii[vis])                                   (train.py:156)
+ *     xyz_gradient_accum[vis] += norm(viewspace_point_tensor.grad[vis, :2]); denom[vis] += 1 (gaussian_model.py:599-602)
+ * with vis = radii > 0 (train.py:131, gaussian_renderer/__init__.py:108).  viewspace_grad is (P,3) float32 (dL_dmeans2D),
+ * radii (P) int32; the three statistics are (P) float32, updated in place; max_radii2D may be NULL. */
+int gsr_densify_stats(int P, const float* viewspace_grad, const int* radii, float* xyz_gradient_accum, float* denom,
+                      float* max_radii2D, void* cuda_stream);
+
+/* ---- densify_and_prune as two calls (scene/gaussian_model.py:558-597 with :366-556) ----
+ * The reference clones, splits and prunes in three rounds of boolean-mask indexing and torch.cat over the six parameter
+ * tensors and their twelve Adam moments (about 60 kernels and a dozen host synchronisations).  Here:
+ *   gsr_densify_classify  reads what the decisions depend on (gradient statistics, raw scaling, raw opacity), writes one
+ *                         flag byte per Gaussian, and leaves the per-block ranks and the five totals on the device;
+ *   gsr_densify_apply     moves every surviving row of every tensor ONCE into its final place in new tensors.
+ * The final order is the reference's: surviving originals, surviving clones, then the N rounds of split children
+ * (round k of parent j uses samples[k * n_split + j], as .repeat(N, 1) lays them out).  Moments of new Gaussians are
+ * zero (cat_tensors_to_optimizer); the three statistics are all zero afterwards (densification_postfix), which also
+ * makes the reference's `max_radii2D > max_screen_size` test always false -- restated as is.
+ * Thresholds are compared in float32 as torch compares a float tensor with a Python scalar:
+ *   clone:  grad >= max_grad  and  max(exp(scaling)) <= percent_dense * extent
+ *   split:  grad >= max_grad  and  max(exp(scaling)) >  percent_dense * extent,   grad = accum / denom, NaN -> 0
+ *   prune:  sigmoid(opacity) < min_opacity  or  (max_screen_size != 0 and max(exp(scaling)) > 0.1 * extent)
+ * children: scaling = log(exp(scaling) * (1 / (0.8 N)))  (torch's CUDA division by a scalar multiplies by the
+ * reciprocal), xyz = R(rotation) samples + xyz with R = build_rotation (utils/general_utils.py:90-114).
+ * totals (5 int32, device): [0] P_out, [1] n_split (rows of `samples` are n_split_copies * n_split), [2] originals kept,
+ * [3] clones kept, [4] split parents whose children are kept.  The caller reads totals back (the one host
+ * synchronisation), draws `samples` = torch.normal(0, exp(scaling)[split].repeat(N,1)) as the reference does, allocates the
+ * outputs with P_out rows and calls gsr_densify_apply with the same scratch. */
+#define GSR_DENSIFY_ORIG_KEEP 1u   /* flag bits */
+#define GSR_DENSIFY_CLONE_KEEP 2u
+#define GSR_DENSIFY_CHILD_KEEP 4u
+#define GSR_DENSIFY_CLONE_SEL 8u
+#define GSR_DENSIFY_SPLIT_SEL 16u
+typedef struct gsr_densify_params {
+    double max_grad, min_opacity, extent, percent_dense;   /* opt.densify_grad_threshold, 0.005, scene.cameras_extent, opt.percent_dense */
+    double max_screen_size;                                /* size_threshold of train.py:161 (0 = None) */
+    int n_split_copies;                                    /* N of densify_and_split (2) */
+} gsr_densify_params;
+typedef struct gsr_densify_group {
+    const float* param; const float* exp_avg; const float* exp_avg_sq;      /* (P, row_width) in; moments may both be NULL */
+    float* param_out; float* exp_avg_out; float* exp_avg_sq_out;            /* (P_out, row_width) out, distinct from the inputs */
+    int row_width;
+} gsr_densify_group;
+size_t gsr_densify_scratch_bytes(int P);
+int gsr_densify_classify(int P, const float* xyz_gradient_accum, const float* denom, const float* scaling_raw,
+                         const float* opacity_raw, const gsr_densify_params* params, unsigned char* flags /* (P) out */,
+                         int* totals /* (5) device out */, char* scratch, void* cuda_stream);
+/* groups: n_groups <= 8 tensors sharing the row index; xyz_group / scaling_group / rotation_group say which of them
+ * are _xyz (3), _scaling (3), _rotation (4).  samples: (n_split_copies * n_split, 3).  totals_host: the five values
+ * read back from the device.  Nothing is written beyond row totals_host[0] of any output. */
+int gsr_densify_apply(int P, const unsigned char* flags, const char* scratch, const int* totals_host,
+                      const gsr_densify_params* params, const float* samples, const gsr_densify_group* groups, int n_groups,
+                      int xyz_group, int scaling_group, int rotation_group, void* cuda_stream);
+
 /* ---- Mean squared distance to the 3 nearest neighbours ----
  * Replaces distCUDA2 of the reference's simple-knn extension (submodules/simple-knn/spatial.cu:15-26, SimpleKNN::knn,
  * simple_knn.cu:185-221), used by GaussianModel.create_from_pcd to initialise the scales (scene/gaussian_model.py:207).

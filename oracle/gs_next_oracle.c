@@ -168,3 +168,203 @@ int gno_knn_mean_d2(int P, const float* points /* (P,3) */, float* mean_d2 /* (P
     free(order);
     return 0;
 }
+
+/* ===============================================================================================================
+ * Densification (second half): the reference's OWN sequence, round by round, on growing arrays --
+ * deliberately not the product's one-pass formulation, so that agreement between the two checks the collapse of the
+ * three rounds into per-original decisions.
+ * Parity pinning: tests/golden/ref_densify_cpu.npz holds inputs, the recorded torch.normal samples and the outputs of the
+ * reference's unmodified GaussianModel.densify_and_prune / add_densification_stats (scene/gaussian_model.py:558-602), run
+ * on the CPU by tests/golden/make_golden_densify.py (the reference hard-codes device="cuda"; the script maps that device
+ * name to the CPU and changes nothing else).  tests/test_densify_cpu.py checks these functions against that file:
+ * selections, order and copied values exactly, computed values (child xyz / scaling) to 1e-6.
+ * Arithmetic notes: torch's CUDA division by a Python scalar multiplies by the float32 reciprocal (BinaryDivTrueKernel.cu),
+ * restated here as exp(s) * (1.0f / (float)(0.8 N)); the CPU run of the reference divides, which differs by at most 1 ulp.
+ * =============================================================================================================== */
+typedef struct {
+    int P, ng, has_state;
+    int w[8];
+    float* p[8]; float* m[8]; float* v[8];
+} gno_model_t;
+
+static float gno_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }
+static float gno_max3(const float* s) { float a = expf(s[0]), b = expf(s[1]), c = expf(s[2]); float m = a > b ? a : b; return m > c ? m : c; }
+
+/* rows with mask != 0 survive: _prune_optimizer (scene/gaussian_model.py:394-419) */
+static void gno_select(gno_model_t* M, const unsigned char* keep) {
+    int n = 0;
+    for (int i = 0; i < M->P; i++) n += keep[i] != 0;
+    for (int g = 0; g < M->ng; g++) {
+        const int w = M->w[g];
+        float** arrs[3] = {&M->p[g], &M->m[g], &M->v[g]};
+        for (int a = 0; a < (M->has_state ? 3 : 1); a++) {
+            float* src = *arrs[a];
+            float* dst = (float*)malloc(sizeof(float) * (size_t)(n > 0 ? n : 1) * w);
+            size_t o = 0;
+            for (int i = 0; i < M->P; i++)
+                if (keep[i]) { memcpy(dst + o, src + (size_t)i * w, sizeof(float) * w); o += w; }
+            free(src);
+            *arrs[a] = dst;
+        }
+    }
+    M->P = n;
+}
+
+/* cat_tensors_to_optimizer (scene/gaussian_model.py:445-470): parameters extended, moments extended with zeros */
+static void gno_cat(gno_model_t* M, float* const* ext, int n_new) {
+    for (int g = 0; g < M->ng; g++) {
+        const size_t w = M->w[g], old = (size_t)M->P * w, add = (size_t)n_new * w;
+        M->p[g] = (float*)realloc(M->p[g], sizeof(float) * (old + add + 1));
+        memcpy(M->p[g] + old, ext[g], sizeof(float) * add);
+        if (M->has_state) {
+            M->m[g] = (float*)realloc(M->m[g], sizeof(float) * (old + add + 1));
+            M->v[g] = (float*)realloc(M->v[g], sizeof(float) * (old + add + 1));
+            memset(M->m[g] + old, 0, sizeof(float) * add);
+            memset(M->v[g] + old, 0, sizeof(float) * add);
+        }
+    }
+    M->P += n_new;
+}
+
+/* build_rotation (utils/general_utils.py:90-114) then bmm with one sample and the parent's position (gaussian_model.py:519-520) */
+static void gno_child_xyz(const float* r4, const float* xyz, const float* smp, float* out) {
+    const float n = sqrtf(r4[0] * r4[0] + r4[1] * r4[1] + r4[2] * r4[2] + r4[3] * r4[3]);
+    const float r = r4[0] / n, x = r4[1] / n, y = r4[2] / n, z = r4[3] / n;
+    const float R[9] = {1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+                        2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+                        2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)};
+    for (int c = 0; c < 3; c++)
+        out[c] = fmaf(R[3 * c + 2], smp[2], fmaf(R[3 * c + 1], smp[1], R[3 * c] * smp[0])) + xyz[c];
+}
+
+/* The two selection masks of densify_and_clone / densify_and_split for the P original Gaussians (the split mask is
+ * evaluated by the reference on the P + n_clone rows after cloning, with zero gradients for the clones: none of those can
+ * be selected).  Returns n_split; the caller draws torch.normal(0, exp(scaling)[split].repeat(N,1)) from it. */
+int gno_densify_masks(int P, const float* accum, const float* denom, const float* scaling, double max_grad, double extent,
+                      double percent_dense, unsigned char* clone_mask, unsigned char* split_mask) {
+    const float thr = (float)max_grad, dense = (float)(percent_dense * extent);
+    int ns = 0;
+    for (int i = 0; i < P; i++) {
+        float g = accum[i] / denom[i];
+        if (isnan(g)) g = 0.f;
+        const float smax = gno_max3(scaling + 3 * (size_t)i);
+        clone_mask[i] = sqrtf(g * g) >= thr && smax <= dense;
+        split_mask[i] = g >= thr && smax > dense;
+        ns += split_mask[i];
+    }
+    return ns;
+}
+
+/* densify_and_prune (scene/gaussian_model.py:558-597).  params / exp_avg / exp_avg_sq: ng arrays of (P, widths[g]);
+ * exp_avg may be NULL (optimizer without state).  Group roles by index.  samples: (N * n_split, 3) as gno_densify_masks
+ * counted them.  Outputs are written into caller arrays of `capacity` rows (P + n_clone + N * n_split always suffices).
+ * Returns the new number of Gaussians, or -1 when capacity is too small. */
+int gno_densify_and_prune(int P, int ng, const int* widths, const float* const* params, const float* const* exp_avg,
+                          const float* const* exp_avg_sq, const float* accum, const float* denom, double max_grad,
+                          double min_opacity, double extent, double percent_dense, double max_screen_size, int N,
+                          const float* samples, int xyz_g, int scaling_g, int rotation_g, int opacity_g, int capacity,
+                          float* const* params_out, float* const* exp_avg_out, float* const* exp_avg_sq_out) {
+    gno_model_t M;
+    M.P = P; M.ng = ng; M.has_state = exp_avg != NULL;
+    for (int g = 0; g < ng; g++) {
+        const size_t n = (size_t)P * widths[g];
+        M.w[g] = widths[g];
+        M.p[g] = (float*)malloc(sizeof(float) * (n + 1)); memcpy(M.p[g], params[g], sizeof(float) * n);
+        M.m[g] = M.v[g] = NULL;
+        if (M.has_state) {
+            M.m[g] = (float*)malloc(sizeof(float) * (n + 1)); memcpy(M.m[g], exp_avg[g], sizeof(float) * n);
+            M.v[g] = (float*)malloc(sizeof(float) * (n + 1)); memcpy(M.v[g], exp_avg_sq[g], sizeof(float) * n);
+        }
+    }
+    const float thr = (float)max_grad, dense = (float)(percent_dense * extent);
+    float* grads = (float*)malloc(sizeof(float) * (size_t)(P + 1));
+    for (int i = 0; i < P; i++) { float g = accum[i] / denom[i]; grads[i] = isnan(g) ? 0.f : g; }          /* :566-567 */
+
+    /* ---- densify_and_clone (:538-556) ---- */
+    {
+        unsigned char* sel = (unsigned char*)calloc((size_t)P + 1, 1);
+        int n = 0;
+        for (int i = 0; i < P; i++) { sel[i] = sqrtf(grads[i] * grads[i]) >= thr && gno_max3(M.p[scaling_g] + 3 * (size_t)i) <= dense; n += sel[i]; }
+        float* ext[8];
+        for (int g = 0; g < ng; g++) {
+            const int w = M.w[g];
+            ext[g] = (float*)malloc(sizeof(float) * ((size_t)n * w + 1));
+            size_t o = 0;
+            for (int i = 0; i < P; i++) if (sel[i]) { memcpy(ext[g] + o, M.p[g] + (size_t)i * w, sizeof(float) * w); o += w; }
+        }
+        gno_cat(&M, ext, n);
+        for (int g = 0; g < ng; g++) free(ext[g]);
+        free(sel);
+    }
+
+    /* ---- densify_and_split (:497-536) ---- */
+    {
+        const int n_init = M.P;
+        float* padded = (float*)calloc((size_t)n_init + 1, sizeof(float));
+        memcpy(padded, grads, sizeof(float) * (size_t)P);
+        unsigned char* sel = (unsigned char*)calloc((size_t)n_init + 1, 1);
+        int ns = 0;
+        for (int i = 0; i < n_init; i++) { sel[i] = padded[i] >= thr && gno_max3(M.p[scaling_g] + 3 * (size_t)i) > dense; ns += sel[i]; }
+        int* idx = (int*)malloc(sizeof(int) * (size_t)(ns + 1));
+        for (int i = 0, j = 0; i < n_init; i++) if (sel[i]) idx[j++] = i;
+        const int n_new = N * ns;
+        const float inv = 1.0f / (float)(0.8 * N);
+        float* ext[8];
+        for (int g = 0; g < ng; g++) {
+            const int w = M.w[g];
+            ext[g] = (float*)malloc(sizeof(float) * ((size_t)n_new * w + 1));
+            for (int j = 0; j < n_new; j++) {                                  /* .repeat(N, 1): row j comes from parent j mod ns */
+                const int par = idx[j % (ns > 0 ? ns : 1)];
+                float* d = ext[g] + (size_t)j * w;
+                if (g == xyz_g) gno_child_xyz(M.p[rotation_g] + 4 * (size_t)par, M.p[xyz_g] + 3 * (size_t)par, samples + 3 * (size_t)j, d);
+                else if (g == scaling_g) for (int c = 0; c < 3; c++) d[c] = logf(expf(M.p[g][3 * (size_t)par + c]) * inv);
+                else memcpy(d, M.p[g] + (size_t)par * w, sizeof(float) * w);
+            }
+        }
+        gno_cat(&M, ext, n_new);
+        for (int g = 0; g < ng; g++) free(ext[g]);
+        unsigned char* keep = (unsigned char*)malloc((size_t)M.P + 1);         /* prune_filter = cat(selected, zeros) -> keep = ~filter */
+        for (int i = 0; i < M.P; i++) keep[i] = !(i < n_init && sel[i]);
+        gno_select(&M, keep);
+        free(keep); free(idx); free(sel); free(padded);
+    }
+
+    /* ---- final prune (:577-593); max_radii2D was reset to zeros by densification_postfix (:493-495) ---- */
+    {
+        const float min_op = (float)min_opacity, big = (float)(0.1 * extent), mss = (float)max_screen_size;
+        unsigned char* keep = (unsigned char*)malloc((size_t)M.P + 1);
+        for (int i = 0; i < M.P; i++) {
+            int prune = gno_sigmoid(M.p[opacity_g][i]) < min_op;
+            if (max_screen_size != 0.0) {
+                const float max_radii2D = 0.f;
+                prune = prune || max_radii2D > mss || gno_max3(M.p[scaling_g] + 3 * (size_t)i) > big;
+            }
+            keep[i] = !prune;
+        }
+        gno_select(&M, keep);
+        free(keep);
+    }
+    free(grads);
+    int ret = M.P;
+    if (M.P > capacity) ret = -1;
+    for (int g = 0; g < ng; g++) {
+        const size_t n = (size_t)M.P * M.w[g];
+        if (ret >= 0) {
+            memcpy(params_out[g], M.p[g], sizeof(float) * n);
+            if (M.has_state) { memcpy(exp_avg_out[g], M.m[g], sizeof(float) * n); memcpy(exp_avg_sq_out[g], M.v[g], sizeof(float) * n); }
+        }
+        free(M.p[g]); free(M.m[g]); free(M.v[g]);
+    }
+    return ret;
+}
+
+/* train.py:153-158 + add_densification_stats (scene/gaussian_model.py:599-602), visibility = radii > 0 */
+void gno_densify_stats(int P, const float* vs_grad /* (P,3) */, const int* radii, float* accum, float* denom, float* max_radii2D) {
+    for (int i = 0; i < P; i++) {
+        if (radii[i] <= 0) continue;
+        const float gx = vs_grad[3 * (size_t)i], gy = vs_grad[3 * (size_t)i + 1];
+        if (max_radii2D) max_radii2D[i] = fmaxf(max_radii2D[i], (float)radii[i]);
+        accum[i] += sqrtf(fmaf(gy, gy, gx * gx));
+        denom[i] += 1.0f;
+    }
+}

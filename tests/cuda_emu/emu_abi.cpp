@@ -17,6 +17,7 @@ GSR_EMU_DEFINE_CUDART
 #include "_gen/gsr_loss.cpp"
 #include "_gen/gsr_adam.cpp"
 #include "_gen/gsr_knn.cpp"
+#include "_gen/gsr_densify.cpp"
 
 // csrc/gsr_exchange.cu is NVLS multimem PTX (multi-GPU only): not emulated
 namespace gsr {

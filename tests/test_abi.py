@@ -256,6 +256,61 @@ def test_adam_and_knn_entry_points_check_their_arguments(lib):
     assert lib.gsr_knn_mean_dist2(5, C.c_void_p(0x1000), C.c_void_p(0x2000), C.c_void_p(0x3010), None) == 1   # scratch alignment
 
 
+class DensifyParams(C.Structure):
+    _fields_ = [("max_grad", C.c_double), ("min_opacity", C.c_double), ("extent", C.c_double), ("percent_dense", C.c_double),
+                ("max_screen_size", C.c_double), ("n_split_copies", C.c_int)]
+
+
+class DensifyGroup(C.Structure):
+    _fields_ = [("param", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p), ("param_out", C.c_void_p),
+                ("exp_avg_out", C.c_void_p), ("exp_avg_sq_out", C.c_void_p), ("row_width", C.c_int)]
+
+
+def densify_argtypes(lib):
+    lib.gsr_densify_scratch_bytes.restype = C.c_size_t
+    lib.gsr_densify_scratch_bytes.argtypes = [C.c_int]
+    lib.gsr_densify_stats.argtypes = [C.c_int] + [C.c_void_p] * 6
+    lib.gsr_densify_classify.argtypes = [C.c_int] + [C.c_void_p] * 9
+    lib.gsr_densify_apply.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int,
+                                      C.c_int, C.c_int, C.c_int, C.c_void_p]
+
+
+def test_densify_entry_points_check_their_arguments(lib):
+    densify_argtypes(lib)
+    A = lambda x: C.c_void_p(x)
+    assert lib.gsr_densify_scratch_bytes(0) == 0 and lib.gsr_densify_scratch_bytes(1000) >= 4 * 4 * 4
+    assert lib.gsr_densify_scratch_bytes(1000) % 256 == 0
+    assert lib.gsr_densify_stats(0, None, None, None, None, None, None) == 0
+    assert lib.gsr_densify_stats(-1, None, None, None, None, None, None) == 1
+    assert lib.gsr_densify_stats(4, A(0x100), None, A(0x100), A(0x100), None, None) == 1          # radii missing
+    ok = DensifyParams(0.0002, 0.005, 3.0, 0.01, 20.0, 2)
+    assert lib.gsr_densify_classify(5, A(0x100), A(0x100), A(0x100), A(0x100), None, A(0x100), A(0x100), A(0x100), None) == 1
+    bad = DensifyParams(0.0002, 0.005, 3.0, 0.01, 20.0, 0)
+    assert lib.gsr_densify_classify(5, A(0x100), A(0x100), A(0x100), A(0x100), C.byref(bad), A(0x100), A(0x100), A(0x100), None) == 1
+    assert b"n_split_copies" in lib.gsr_last_error()
+    assert lib.gsr_densify_classify(5, A(0x100), A(0x100), A(0x100), A(0x100), C.byref(ok), A(0x100), A(0x100), A(0x110), None) == 1
+    assert b"aligned" in lib.gsr_last_error()
+    assert lib.gsr_densify_classify(5, None, A(0x100), A(0x100), A(0x100), C.byref(ok), A(0x100), A(0x100), A(0x100), None) == 1
+    # apply: totals must be consistent with one another and with P; roles must point at groups of the right width
+    groups = (DensifyGroup * 3)()
+    for g, w in zip(groups, (3, 3, 4)):
+        g.param, g.param_out, g.row_width = 0x1000, 0x2000, w
+    tot = (C.c_int * 5)(7, 1, 4, 1, 1)
+    args = lambda t=tot, grp=groups, n=3, roles=(0, 1, 2), smp=A(0x3000): (10, A(0x100), A(0x100), t, C.byref(ok), smp, grp, n, *roles, None)
+    assert lib.gsr_densify_apply(0, None, None, None, C.byref(ok), None, None, 0, 0, 0, 0, None) == 0
+    assert lib.gsr_densify_apply(*args(t=(C.c_int * 5)(8, 1, 4, 1, 1))) == 1 and b"totals" in lib.gsr_last_error()
+    assert lib.gsr_densify_apply(*args(t=(C.c_int * 5)(7, 0, 4, 1, 1))) == 1                      # kept children without split parents
+    assert lib.gsr_densify_apply(*args(roles=(0, 1, 1))) == 1 and b"row widths" in lib.gsr_last_error()
+    assert lib.gsr_densify_apply(*args(roles=(0, 0, 2))) == 1
+    assert lib.gsr_densify_apply(*args(smp=None)) == 1 and b"samples" in lib.gsr_last_error()
+    assert lib.gsr_densify_apply(*args(n=9)) == 1
+    groups[1].exp_avg = 0x4000                                                                      # a moment without its pair
+    assert lib.gsr_densify_apply(*args()) == 1 and b"pairs" in lib.gsr_last_error()
+    groups[1].exp_avg = None
+    groups[2].param_out = groups[2].param                                                           # in place is not supported
+    assert lib.gsr_densify_apply(*args()) == 1 and b"alias" in lib.gsr_last_error()
+
+
 def test_launch_counter_starts_at_zero_on_cpu(lib):
     lib.gsr_launch_count.restype = C.c_ulonglong
     assert lib.gsr_launch_count() == 0

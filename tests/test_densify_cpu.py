@@ -1,0 +1,225 @@
+"""Densification (second half) on the CPU: the oracle against the fixture written by the reference's own
+GaussianModel (tests/golden/make_golden_densify.py), and -- through the host-emulated C ABI (tests/cuda_emu) -- the
+product's classify / apply / stats kernels against the oracle, bit for bit."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from oracle import gs_next_oracle as O   # noqa: E402
+
+GOLD = np.load(os.path.join(ROOT, "tests", "golden", "ref_densify_cpu.npz"))
+NAMES = O.GROUP_ORDER
+
+
+def _case(tag):
+    g = lambda k: GOLD[f"{tag}_{k}"]
+    has = bool(g("with_moments"))
+    before = {n: g("before_p_" + n) for n in NAMES}
+    m = {n: g("before_m_" + n) for n in NAMES} if has else None
+    v = {n: g("before_v_" + n) for n in NAMES} if has else None
+    after = {n: g("after_p_" + n) for n in NAMES}
+    am = {n: g("after_m_" + n) for n in NAMES} if has else None
+    av = {n: g("after_v_" + n) for n in NAMES} if has else None
+    args = dict(max_grad=float(g("max_grad")), min_opacity=float(g("min_opacity")), extent=float(g("extent")),
+                percent_dense=float(g("percent_dense")), max_screen_size=float(g("max_screen_size")))
+    return before, m, v, g("before_accum"), g("before_denom"), g("samples"), args, after, am, av, g
+
+
+@pytest.mark.parametrize("tag", list(GOLD["cases"]))
+def test_oracle_reproduces_the_references_densify_and_prune(tag):
+    before, m, v, accum, denom, samples, args, after, am, av, g = _case(tag)
+    p1, m1, v1 = O.densify_and_prune(before, m, v, accum, denom, samples=samples, **args)
+    n = after["xyz"].shape[0]
+    assert n > 0 and p1["xyz"].shape[0] == n
+    for name in NAMES:
+        assert p1[name].shape == after[name].shape, name
+        if name in ("xyz", "scaling"):          # children are computed: bmm order / division vs reciprocal, <= a few ulp
+            np.testing.assert_allclose(p1[name], after[name], rtol=2e-6, atol=2e-6, err_msg=name)
+        else:                                    # copied rows: exact, in the reference's order
+            assert np.array_equal(p1[name], after[name]), name
+        if m is not None:
+            assert np.array_equal(m1[name], am[name]) and np.array_equal(v1[name], av[name]), name
+    # rows that are not split children are copies of xyz / scaling as well: exact
+    n_child = samples.shape[0]
+    if n_child < n:
+        head = n - n_child          # children, if any survive, are at the end; at least the first n - n_child rows are copies
+        assert np.array_equal(p1["xyz"][:head], after["xyz"][:head]) and np.array_equal(p1["scaling"][:head], after["scaling"][:head])
+    # the statistics are all zeros afterwards (densification_postfix), of the new length
+    for k in ("accum", "denom", "max_radii2D"):
+        assert g("after_" + k).shape[0] == n and not g("after_" + k).any()
+
+
+def test_oracle_reproduces_the_references_statistics_update():
+    s = lambda k: GOLD["stats_" + k]
+    accum, denom, mr = s("accum0").reshape(-1).copy(), s("denom0").reshape(-1).copy(), s("max_radii0").copy()
+    O.densify_stats(s("vs_grad"), s("radii"), accum, denom, mr)
+    assert np.array_equal(denom, s("denom1").reshape(-1)) and np.array_equal(mr, s("max_radii1"))
+    np.testing.assert_allclose(accum, s("accum1").reshape(-1), rtol=2e-7, atol=0)      # 2-element norm: fma or not, 1 ulp
+    untouched = s("radii") <= 0
+    assert untouched.any() and np.array_equal(accum[untouched], s("accum0").reshape(-1)[untouched])
+
+
+# ---- the product's kernels (host-emulated C ABI) against the oracle ---------------------------------------------------------
+import ctypes as C   # noqa: E402
+
+from test_abi import DensifyGroup, DensifyParams, densify_argtypes   # noqa: E402
+
+WIDTHS = {"xyz": 3, "f_dc": 3, "f_rest": 45, "opacity": 1, "scaling": 3, "rotation": 4}
+
+
+@pytest.fixture(scope="module")
+def abi():
+    sys.path.insert(0, os.path.join(ROOT, "tests", "cuda_emu"))
+    import build_emu
+    lib = C.CDLL(os.environ.get("GSR_EMU_ABI_SO") or build_emu.build("emu_abi"))
+    lib.gsr_last_error.restype = C.c_char_p
+    densify_argtypes(lib)
+    return lib
+
+
+def _ptr(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def _aligned_bytes(n):
+    raw = np.zeros(n + 512, np.uint8)
+    off = (-raw.ctypes.data) % 256
+    return raw, raw.ctypes.data + off
+
+
+def densify_through_abi(lib, params, m, v, accum, denom, args, draw_samples, N=2, names=NAMES):
+    """classify -> read totals -> draw samples -> apply, as gsr_densify.densify_and_prune drives the library.
+    draw_samples(split_mask) -> (N * n_split, 3).  Returns (params', m', v', flags, totals)."""
+    P = params["xyz"].shape[0]
+    flat = lambda a: np.ascontiguousarray(a, np.float32).reshape(P, -1)
+    p = {n: flat(params[n]) for n in names}
+    has = m is not None
+    mm = {n: flat(m[n]) for n in names} if has else None
+    vv = {n: flat(v[n]) for n in names} if has else None
+    prm = DensifyParams(args["max_grad"], args["min_opacity"], args["extent"], args["percent_dense"], args["max_screen_size"] or 0.0, N)
+    flags = np.zeros(max(P, 1), np.uint8)
+    totals = np.full(5, -1, np.int32)
+    keep, scratch = _aligned_bytes(lib.gsr_densify_scratch_bytes(P))
+    a, d = (np.ascontiguousarray(x, np.float32).reshape(-1) for x in (accum, denom))
+    rc = lib.gsr_densify_classify(P, _ptr(a), _ptr(d), _ptr(p["scaling"]), _ptr(p["opacity"]), C.byref(prm), _ptr(flags), _ptr(totals),
+                                  C.c_void_p(scratch), None)
+    assert rc == 0, lib.gsr_last_error()
+    P_out, n_split = int(totals[0]), int(totals[1])
+    samples = np.ascontiguousarray(draw_samples((flags[:P] & 16) != 0), np.float32).reshape(-1, 3)
+    assert samples.shape[0] == N * n_split
+    groups = (DensifyGroup * len(names))()
+    outs = {}
+    for g, n in zip(groups, names):
+        w = p[n].shape[1]
+        po = np.full((P_out + 1, w), np.nan, np.float32)            # one guard row: nothing may be written beyond P_out
+        mo = np.full((P_out + 1, w), np.nan, np.float32) if has else None
+        vo = np.full((P_out + 1, w), np.nan, np.float32) if has else None
+        outs[n] = (po, mo, vo)
+        g.param, g.param_out, g.row_width = p[n].ctypes.data, po.ctypes.data, w
+        if has:
+            g.exp_avg, g.exp_avg_sq, g.exp_avg_out, g.exp_avg_sq_out = mm[n].ctypes.data, vv[n].ctypes.data, mo.ctypes.data, vo.ctypes.data
+    rc = lib.gsr_densify_apply(P, _ptr(flags), C.c_void_p(scratch), _ptr(totals), C.byref(prm), _ptr(samples), groups, len(names),
+                               names.index("xyz"), names.index("scaling"), names.index("rotation"), None)
+    assert rc == 0, lib.gsr_last_error()
+    for n in names:
+        for arr in outs[n]:
+            if arr is not None:
+                assert np.isnan(arr[P_out]).all(), "guard row of %s written" % n
+                assert np.isfinite(arr[:P_out]).all(), "unwritten element in %s" % n
+    shape = lambda n, x: x[:P_out].reshape((P_out,) + tuple(params[n].shape[1:]))
+    pick = lambda k: {n: shape(n, outs[n][k]) for n in names}
+    return pick(0), (pick(1) if has else None), (pick(2) if has else None), flags[:P], totals
+
+
+@pytest.mark.parametrize("tag", list(GOLD["cases"]))
+def test_emulated_kernels_equal_the_oracle_on_the_reference_fixture(abi, tag):
+    before, m, v, accum, denom, samples, args, after, am, av, g = _case(tag)
+    p1, m1, v1, flags, totals = densify_through_abi(abi, before, m, v, accum, denom, args, lambda split: samples)
+    p0, m0, v0 = O.densify_and_prune(before, m, v, accum, denom, samples=samples, **args)
+    cm, sm = O.densify_masks(accum.reshape(-1), denom.reshape(-1), before["scaling"], args["max_grad"], args["extent"], args["percent_dense"])
+    assert np.array_equal((flags & 8) != 0, cm) and np.array_equal((flags & 16) != 0, sm)
+    assert totals[0] == after["xyz"].shape[0] and totals[1] == sm.sum()
+    for name in NAMES:                                   # same host libm on both sides: bit for bit, every tensor
+        assert np.array_equal(p1[name], p0[name]), name
+        if m is not None:
+            assert np.array_equal(m1[name], m0[name]) and np.array_equal(v1[name], v0[name]), name
+        # and against the reference's own output, as the oracle is pinned
+        if name in ("xyz", "scaling"):
+            np.testing.assert_allclose(p1[name], after[name], rtol=2e-6, atol=2e-6)
+        else:
+            assert np.array_equal(p1[name], after[name]), name
+
+
+def _random_model(rng, P, with_moments=True):
+    p = {n: rng.normal(size=(P, WIDTHS[n])).astype(np.float32) for n in NAMES}
+    p["opacity"] = (p["opacity"] * 3 - 1).astype(np.float32)
+    p["scaling"] = (p["scaling"] * 1.2 - 3.5).astype(np.float32)
+    m = {n: (rng.normal(size=p[n].shape) * 1e-3).astype(np.float32) for n in NAMES} if with_moments else None
+    v = {n: (rng.random(size=p[n].shape) * 1e-6).astype(np.float32) for n in NAMES} if with_moments else None
+    denom = (rng.integers(1, 40, P) * (rng.random(P) > 0.15)).astype(np.float32)
+    accum = (rng.random(P) * 6e-4 * denom).astype(np.float32)
+    return p, m, v, accum, denom
+
+
+@pytest.mark.parametrize("P,N,screen,with_moments", [(1, 2, 20.0, True), (255, 2, 20.0, True), (256, 2, 0.0, False), (257, 3, 20.0, True),
+                                                     (1531, 2, 20.0, True), (2048, 1, 20.0, True)])
+def test_emulated_kernels_equal_the_oracle_on_random_models(abi, P, N, screen, with_moments):
+    """Block boundaries (256 rows per block), several blocks of offsets, N = 1..3 children, with and without Adam state."""
+    rng = np.random.default_rng(P * 7 + N)
+    p, m, v, accum, denom = _random_model(rng, P, with_moments)
+    args = dict(max_grad=0.0002, min_opacity=0.005, extent=3.0, percent_dense=0.01, max_screen_size=screen)
+    drawn = {}
+    def draw(split):
+        drawn["s"] = (rng.normal(size=(N * int(split.sum()), 3)) * np.tile(np.exp(p["scaling"][split]), (N, 1))).astype(np.float32)
+        return drawn["s"]
+    p1, m1, v1, flags, totals = densify_through_abi(abi, p, m, v, accum, denom, args, draw, N=N)
+    p0, m0, v0 = O.densify_and_prune(p, m, v, accum, denom, samples=drawn["s"], N=N, **args)
+    assert totals[0] == p0["xyz"].shape[0]
+    for name in NAMES:
+        assert np.array_equal(p1[name], p0[name]), name
+        if with_moments:
+            assert np.array_equal(m1[name], m0[name]) and np.array_equal(v1[name], v0[name]), name
+
+
+def test_emulated_extremes_nothing_selected_everything_pruned_everything_split(abi):
+    rng = np.random.default_rng(5)
+    P = 300
+    p, m, v, accum, denom = _random_model(rng, P)
+    base = dict(min_opacity=0.005, extent=3.0, percent_dense=0.01, max_screen_size=20.0)
+    cases = {"nothing selected": dict(base, max_grad=1e9), "all pruned": dict(base, max_grad=1e9, min_opacity=2.0),
+             "all hot": dict(base, max_grad=-1.0, percent_dense=1e-9, max_screen_size=0.0, min_opacity=0.0)}
+    for what, args in cases.items():
+        drawn = {}
+        def draw(split):
+            drawn["s"] = rng.normal(size=(2 * int(split.sum()), 3)).astype(np.float32)
+            return drawn["s"]
+        p1, m1, v1, flags, totals = densify_through_abi(abi, p, m, v, accum, denom, args, draw)
+        p0, m0, v0 = O.densify_and_prune(p, m, v, accum, denom, samples=drawn["s"], **args)
+        assert totals[0] == p0["xyz"].shape[0], what
+        if what == "all pruned":
+            assert totals[0] == 0
+        if what == "all hot":
+            assert totals[1] == P and totals[0] == 2 * P        # every Gaussian is large and hot: all split, parents removed
+        for name in NAMES:
+            assert np.array_equal(p1[name], p0[name]), (what, name)
+            assert np.array_equal(m1[name], m0[name]) and np.array_equal(v1[name], v0[name]), (what, name)
+
+
+def test_emulated_statistics_kernel_equals_the_oracle_and_the_reference(abi):
+    s = lambda k: GOLD["stats_" + k]
+    accum, denom, mr = s("accum0").reshape(-1).copy(), s("denom0").reshape(-1).copy(), s("max_radii0").copy()
+    vs, radii = np.ascontiguousarray(s("vs_grad"), np.float32), np.ascontiguousarray(s("radii"), np.int32)
+    assert abi.gsr_densify_stats(radii.shape[0], _ptr(vs), _ptr(radii), _ptr(accum), _ptr(denom), _ptr(mr), None) == 0, abi.gsr_last_error()
+    a0, d0, r0 = s("accum0").reshape(-1).copy(), s("denom0").reshape(-1).copy(), s("max_radii0").copy()
+    O.densify_stats(vs, radii, a0, d0, r0)
+    assert np.array_equal(accum, a0) and np.array_equal(denom, d0) and np.array_equal(mr, r0)
+    assert np.array_equal(denom, s("denom1").reshape(-1)) and np.array_equal(mr, s("max_radii1"))
+    np.testing.assert_allclose(accum, s("accum1").reshape(-1), rtol=2e-7, atol=0)
+    # max_radii2D is optional
+    a1, d1 = s("accum0").reshape(-1).copy(), s("denom0").reshape(-1).copy()
+    assert abi.gsr_densify_stats(radii.shape[0], _ptr(vs), _ptr(radii), _ptr(a1), _ptr(d1), None, None) == 0
+    assert np.array_equal(a1, a0) and np.array_equal(d1, d0)
