@@ -431,6 +431,94 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         check(gsr_knn_mean_dist2((int)P, pts.data_ptr<float>(), means.data_ptr<float>(), reinterpret_cast<char*>(scratch.data_ptr()), (void*)st));
         return means;
     }, "mean squared distance to the 3 nearest neighbours (include/gsr.h: gsr_knn_mean_dist2; simple-knn's distCUDA2)");
+    m.def("densify_stats", [](const torch::Tensor& viewspace_grad, const torch::Tensor& radii, torch::Tensor& accum, torch::Tensor& denom,
+                              const c10::optional<torch::Tensor>& max_radii2D) {
+        TORCH_CHECK(viewspace_grad.is_cuda(), "densify_stats: CUDA tensors only (there is no CPU path)");
+        const auto dev = viewspace_grad.device();
+        const int64_t P = radii.numel();
+        TORCH_CHECK(viewspace_grad.scalar_type() == torch::kFloat32 && viewspace_grad.is_contiguous() && viewspace_grad.dim() == 2 &&
+                    viewspace_grad.size(0) == P && viewspace_grad.size(1) == 3, "densify_stats: viewspace gradient must be contiguous (P,3) float32");
+        TORCH_CHECK(radii.device() == dev && radii.scalar_type() == torch::kInt32 && radii.is_contiguous(), "densify_stats: radii must be contiguous (P,) int32");
+        for (const torch::Tensor* t : {&accum, &denom})
+            TORCH_CHECK(t->device() == dev && t->scalar_type() == torch::kFloat32 && t->is_contiguous() && t->numel() == P,
+                        "densify_stats: xyz_gradient_accum and denom must be contiguous float32 with P elements");
+        float* mr = nullptr;
+        if (max_radii2D.has_value()) {
+            TORCH_CHECK(max_radii2D->device() == dev && max_radii2D->scalar_type() == torch::kFloat32 && max_radii2D->is_contiguous() &&
+                        max_radii2D->numel() == P, "densify_stats: max_radii2D must be contiguous (P,) float32");
+            mr = max_radii2D->data_ptr<float>();
+        }
+        const c10::cuda::CUDAGuard guard(dev);
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(gsr_densify_stats((int)P, viewspace_grad.data_ptr<float>(), radii.data_ptr<int>(), accum.data_ptr<float>(), denom.data_ptr<float>(), mr, (void*)st));
+    }, "per-iteration densification statistics, in place (include/gsr.h: gsr_densify_stats)",
+          py::arg("viewspace_grad"), py::arg("radii"), py::arg("xyz_gradient_accum"), py::arg("denom"), py::arg("max_radii2D") = py::none());
+    m.def("densify_classify", [](const torch::Tensor& accum, const torch::Tensor& denom, const torch::Tensor& scaling, const torch::Tensor& opacity,
+                                 double max_grad, double min_opacity, double extent, double percent_dense, double max_screen_size, int64_t copies) {
+        TORCH_CHECK(scaling.is_cuda(), "densify_classify: CUDA tensors only (there is no CPU path)");
+        const auto dev = scaling.device();
+        const int64_t P = scaling.size(0);
+        TORCH_CHECK(scaling.dim() == 2 && scaling.size(1) == 3, "densify_classify: scaling must be (P,3)");
+        for (const torch::Tensor* t : {&accum, &denom, &scaling, &opacity})
+            TORCH_CHECK(t->device() == dev && t->scalar_type() == torch::kFloat32 && t->is_contiguous(), "densify_classify: contiguous float32 tensors on one CUDA device");
+        TORCH_CHECK(accum.numel() == P && denom.numel() == P && opacity.numel() == P, "densify_classify: statistics and opacity must have P elements");
+        const c10::cuda::CUDAGuard guard(dev);
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        auto bytes = scaling.options().dtype(torch::kUInt8);
+        torch::Tensor flags = torch::empty({P}, bytes);
+        torch::Tensor scratch = torch::empty({(int64_t)gsr_densify_scratch_bytes((int)P)}, bytes);
+        torch::Tensor totals = torch::empty({5}, scaling.options().dtype(torch::kInt32));
+        gsr_densify_params prm{max_grad, min_opacity, extent, percent_dense, max_screen_size, (int)copies};
+        check(gsr_densify_classify((int)P, accum.data_ptr<float>(), denom.data_ptr<float>(), scaling.data_ptr<float>(), opacity.data_ptr<float>(), &prm,
+                                   flags.data_ptr<uint8_t>(), totals.data_ptr<int>(), reinterpret_cast<char*>(scratch.data_ptr()), (void*)st));
+        return std::make_tuple(flags, totals, scratch);
+    }, "densify_and_prune, first call: (flags, totals, scratch) (include/gsr.h: gsr_densify_classify)");
+    m.def("densify_apply", [](const torch::Tensor& flags, const torch::Tensor& scratch, std::vector<int64_t> totals, const torch::Tensor& samples,
+                              std::vector<torch::Tensor> params, std::vector<c10::optional<torch::Tensor>> exp_avgs,
+                              std::vector<c10::optional<torch::Tensor>> exp_avg_sqs, int64_t xyz_group, int64_t scaling_group, int64_t rotation_group,
+                              double max_grad, double min_opacity, double extent, double percent_dense, double max_screen_size, int64_t copies) {
+        const size_t n = params.size();
+        TORCH_CHECK(n >= 1 && exp_avgs.size() == n && exp_avg_sqs.size() == n && totals.size() == 5, "densify_apply: one exp_avg / exp_avg_sq entry per parameter, five totals");
+        TORCH_CHECK(flags.is_cuda(), "densify_apply: CUDA tensors only (there is no CPU path)");
+        const auto dev = flags.device();
+        const int64_t P = flags.numel(), P_out = totals[0];
+        TORCH_CHECK(samples.device() == dev && samples.scalar_type() == torch::kFloat32 && samples.is_contiguous() && samples.numel() == 3 * copies * totals[1],
+                    "densify_apply: samples must be contiguous (N * n_split, 3) float32");
+        const c10::cuda::CUDAGuard guard(dev);
+        std::vector<gsr_densify_group> groups(n);
+        std::vector<torch::Tensor> out_p(n);
+        std::vector<c10::optional<torch::Tensor>> out_m(n), out_v(n);
+        for (size_t i = 0; i < n; i++) {
+            const torch::Tensor& p = params[i];
+            TORCH_CHECK(p.device() == dev && p.scalar_type() == torch::kFloat32 && p.is_contiguous() && p.dim() >= 1 && p.size(0) == P,
+                        "densify_apply: parameters must be contiguous float32 with P rows");
+            auto shape = p.sizes().vec();
+            shape[0] = P_out;
+            out_p[i] = torch::empty(shape, p.options());
+            groups[i] = gsr_densify_group{p.data_ptr<float>(), nullptr, nullptr, out_p[i].data_ptr<float>(), nullptr, nullptr, (int)(P > 0 ? p.numel() / P : 1)};
+            if (P == 0) { int w = 1; for (size_t d = 1; d < shape.size(); d++) w *= (int)shape[d]; groups[i].row_width = w; }
+            TORCH_CHECK(exp_avgs[i].has_value() == exp_avg_sqs[i].has_value(), "densify_apply: moments come in pairs");
+            if (exp_avgs[i].has_value()) {
+                for (const torch::Tensor* t : {&*exp_avgs[i], &*exp_avg_sqs[i]})
+                    TORCH_CHECK(t->device() == dev && t->scalar_type() == torch::kFloat32 && t->is_contiguous() && t->sizes() == p.sizes(),
+                                "densify_apply: moments must match their parameter");
+                out_m[i] = torch::empty(shape, p.options());
+                out_v[i] = torch::empty(shape, p.options());
+                groups[i].exp_avg = exp_avgs[i]->data_ptr<float>();
+                groups[i].exp_avg_sq = exp_avg_sqs[i]->data_ptr<float>();
+                groups[i].exp_avg_out = out_m[i]->data_ptr<float>();
+                groups[i].exp_avg_sq_out = out_v[i]->data_ptr<float>();
+            }
+        }
+        int th[5];
+        for (int i = 0; i < 5; i++) th[i] = (int)totals[i];
+        gsr_densify_params prm{max_grad, min_opacity, extent, percent_dense, max_screen_size, (int)copies};
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(dev.index()).stream();
+        check(gsr_densify_apply((int)P, flags.data_ptr<uint8_t>(), reinterpret_cast<const char*>(scratch.data_ptr()), th, &prm,
+                                samples.numel() ? samples.data_ptr<float>() : nullptr, groups.data(), (int)n, (int)xyz_group, (int)scaling_group,
+                                (int)rotation_group, (void*)st));
+        return std::make_tuple(out_p, out_m, out_v);
+    }, "densify_and_prune, second call: new (params, exp_avgs, exp_avg_sqs) (include/gsr.h: gsr_densify_apply)");
     m.def("backward_chunk_plan", [](int64_t P) {
         int b[GSR_MAX_CHUNKS + 1];
         const int n = gsr_backward_chunk_plan((int)P, b);

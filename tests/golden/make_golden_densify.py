@@ -102,7 +102,8 @@ def make_case(GaussianModel, opt, seed, P, with_moments, max_screen_size, extent
     case = {"before_" + k: v for k, v in before.items()}
     case.update({"after_" + k: v for k, v in after.items()})
     case.update(samples=drawn[0].numpy(), max_grad=opt.densify_grad_threshold, min_opacity=0.005, extent=extent,
-                percent_dense=g.percent_dense, max_screen_size=float(max_screen_size or 0.0), with_moments=int(with_moments))
+                percent_dense=g.percent_dense, max_screen_size=float(max_screen_size or 0.0), with_moments=int(with_moments),
+                sampling_seed=seed + 1)
     return case
 
 

@@ -223,3 +223,138 @@ def test_emulated_statistics_kernel_equals_the_oracle_and_the_reference(abi):
     a1, d1 = s("accum0").reshape(-1).copy(), s("denom0").reshape(-1).copy()
     assert abi.gsr_densify_stats(radii.shape[0], _ptr(vs), _ptr(radii), _ptr(a1), _ptr(d1), None, None) == 0
     assert np.array_equal(a1, a0) and np.array_equal(d1, d0)
+
+
+# ---- host logic of gsr_densify (the drop-in for GaussianModel.densify_and_prune) -------------------------------------------
+class _EmulatedExtension:
+    """Stands in for the torch extension's three densify entry points with CPU tensors over the host-emulated C ABI, so
+    that the Python glue (optimizer surgery, the sampling call, attribute hand-over) runs here.  Test double only."""
+
+    def __init__(self, lib):
+        self.lib = lib
+
+    def densify_stats(self, grad, radii, accum, denom, max_radii2D=None):
+        tp = lambda t: None if t is None else C.c_void_p(t.data_ptr())
+        assert self.lib.gsr_densify_stats(radii.numel(), tp(grad), tp(radii), tp(accum), tp(denom), tp(max_radii2D), None) == 0
+
+    def densify_classify(self, accum, denom, scaling, opacity, max_grad, min_opacity, extent, percent_dense, screen, copies):
+        import torch
+        P = scaling.shape[0]
+        self.prm = DensifyParams(max_grad, min_opacity, extent, percent_dense, screen, copies)
+        flags = torch.zeros(P, dtype=torch.uint8)
+        totals = torch.zeros(5, dtype=torch.int32)
+        n = self.lib.gsr_densify_scratch_bytes(P)
+        raw = torch.zeros(n + 512, dtype=torch.uint8)
+        off = (-raw.data_ptr()) % 256
+        scratch = raw[off:off + n]
+        tp = lambda t: C.c_void_p(t.data_ptr())
+        rc = self.lib.gsr_densify_classify(P, tp(accum), tp(denom), tp(scaling), tp(opacity), C.byref(self.prm), tp(flags), tp(totals), tp(scratch), None)
+        assert rc == 0, self.lib.gsr_last_error()
+        return flags, totals, scratch
+
+    def densify_apply(self, flags, scratch, totals, samples, params, ms, vs, xyz_g, scaling_g, rotation_g, *hyper):
+        import torch
+        P_out = totals[0]
+        groups = (DensifyGroup * len(params))()
+        out_p, out_m, out_v = [], [], []
+        for g, p, m, v in zip(groups, params, ms, vs):
+            shape = (P_out,) + tuple(p.shape[1:])
+            out_p.append(torch.full(shape, float("nan")))
+            g.param, g.param_out, g.row_width = p.data_ptr(), out_p[-1].data_ptr(), p.numel() // max(p.shape[0], 1)
+            if m is not None:
+                out_m.append(torch.full(shape, float("nan"))); out_v.append(torch.full(shape, float("nan")))
+                g.exp_avg, g.exp_avg_sq, g.exp_avg_out, g.exp_avg_sq_out = m.data_ptr(), v.data_ptr(), out_m[-1].data_ptr(), out_v[-1].data_ptr()
+            else:
+                out_m.append(None); out_v.append(None)
+        th = (C.c_int * 5)(*totals)
+        tp = lambda t: C.c_void_p(t.data_ptr())
+        rc = self.lib.gsr_densify_apply(flags.numel(), tp(flags), tp(scratch), th, C.byref(DensifyParams(*hyper)), tp(samples), groups,
+                                        len(params), xyz_g, scaling_g, rotation_g, None)
+        assert rc == 0, self.lib.gsr_last_error()
+        return out_p, out_m, out_v
+
+
+class _Model:
+    """The attributes of the reference's GaussianModel that densification touches (scene/gaussian_model.py:44-62)."""
+    percent_dense = 0.01
+
+
+def _model_from_fixture(tag, optimizer_cls):
+    import torch
+    before, m, v, accum, denom, samples, args, after, am, av, g = _case(tag)
+    attr = {"xyz": "_xyz", "f_dc": "_features_dc", "f_rest": "_features_rest", "opacity": "_opacity", "scaling": "_scaling", "rotation": "_rotation"}
+    mdl = _Model()
+    for n in NAMES:
+        setattr(mdl, attr[n], torch.nn.Parameter(torch.from_numpy(before[n].copy())))
+    mdl.percent_dense = args["percent_dense"]
+    mdl.optimizer = optimizer_cls([{"params": [getattr(mdl, attr[n])], "lr": 1e-3, "name": n} for n in NAMES], lr=0.0, eps=1e-15)
+    if m is not None:
+        for n in NAMES:
+            mdl.optimizer.state[getattr(mdl, attr[n])] = {"step": torch.tensor(2.0), "exp_avg": torch.from_numpy(m[n].copy()),
+                                                          "exp_avg_sq": torch.from_numpy(v[n].copy())}
+    mdl.xyz_gradient_accum = torch.from_numpy(accum.copy())
+    mdl.denom = torch.from_numpy(denom.copy())
+    mdl.max_radii2D = torch.from_numpy(g("before_max_radii2D").copy())
+    return mdl, attr, args, after, am, av, int(g("sampling_seed"))
+
+
+@pytest.mark.parametrize("tag", list(GOLD["cases"]))
+def test_drop_in_densify_and_prune_reproduces_the_reference_model_including_its_random_draw(abi, tag, monkeypatch):
+    """gsr_densify.densify_and_prune on the fixture's model, seeded like the reference run: the samples it draws are the
+    ones the reference drew (same torch.normal call), and model + optimizer end up as the reference's."""
+    import torch
+    import gsr_densify
+    monkeypatch.setattr(gsr_densify, "_C", _EmulatedExtension(abi))
+    mdl, attr, args, after, am, av, seed = _model_from_fixture(tag, torch.optim.Adam)
+    torch.manual_seed(seed)
+    P0, P1, n_clone, n_split = gsr_densify.densify_and_prune(mdl, args["max_grad"], args["min_opacity"], args["extent"],
+                                                             args["max_screen_size"] or None)
+    assert P1 == after["xyz"].shape[0] and n_split * 2 == GOLD[f"{tag}_samples"].shape[0]
+    assert [g["name"] for g in mdl.optimizer.param_groups] == list(NAMES)
+    for n in NAMES:
+        p = getattr(mdl, attr[n])
+        assert isinstance(p, torch.nn.Parameter) and p.requires_grad and mdl.optimizer.param_groups[NAMES.index(n)]["params"][0] is p
+        got = p.detach().numpy()
+        assert got.shape == after[n].shape
+        if n in ("xyz", "scaling"):
+            np.testing.assert_allclose(got, after[n], rtol=2e-6, atol=2e-6)
+        else:
+            assert np.array_equal(got, after[n]), n
+        if am is not None:
+            st = mdl.optimizer.state[p]
+            assert float(st["step"]) == 2.0 and len(mdl.optimizer.state) == len(NAMES)
+            assert np.array_equal(st["exp_avg"].numpy(), am[n]) and np.array_equal(st["exp_avg_sq"].numpy(), av[n])
+        else:
+            assert len(mdl.optimizer.state) == 0
+    assert mdl.xyz_gradient_accum.shape == (P1, 1) and mdl.denom.shape == (P1, 1) and mdl.max_radii2D.shape == (P1,)
+    assert not mdl.xyz_gradient_accum.any() and not mdl.denom.any() and not mdl.max_radii2D.any()
+    # the optimizer still steps on the new parameters
+    for n in NAMES:
+        getattr(mdl, attr[n]).grad = torch.ones_like(getattr(mdl, attr[n]))
+    mdl.optimizer.step()
+
+
+def test_drop_in_statistics_update_matches_the_reference(abi, monkeypatch):
+    import torch
+    import gsr_densify
+    monkeypatch.setattr(gsr_densify, "_C", _EmulatedExtension(abi))
+    s = lambda k: GOLD["stats_" + k]
+    mdl = _Model()
+    mdl.xyz_gradient_accum, mdl.denom = torch.from_numpy(s("accum0").copy()), torch.from_numpy(s("denom0").copy())
+    mdl.max_radii2D = torch.from_numpy(s("max_radii0").copy())
+    vsp = torch.zeros(s("vs_grad").shape, requires_grad=True)
+    vsp.grad = torch.from_numpy(s("vs_grad").copy())
+    gsr_densify.add_densification_stats(mdl, vsp, torch.from_numpy(s("radii").copy()))
+    assert np.array_equal(mdl.denom.numpy(), s("denom1")) and np.array_equal(mdl.max_radii2D.numpy(), s("max_radii1"))
+    np.testing.assert_allclose(mdl.xyz_gradient_accum.numpy(), s("accum1"), rtol=2e-7, atol=0)
+
+
+def test_drop_in_refuses_host_tensors_without_the_test_double():
+    """The real extension has no CPU path: host tensors are rejected, nothing is computed."""
+    import torch
+    import gsr_densify
+    mdl, attr, args, *_ = _model_from_fixture("a", torch.optim.Adam)
+    with pytest.raises(RuntimeError, match="CUDA tensors only"):
+        gsr_densify.densify_and_prune(mdl, args["max_grad"], args["min_opacity"], args["extent"], 20)
+    with pytest.raises(RuntimeError, match="CUDA tensors only"):
+        gsr_densify.add_densification_stats(mdl, torch.zeros(mdl._xyz.shape[0], 3), torch.ones(mdl._xyz.shape[0], dtype=torch.int32))
