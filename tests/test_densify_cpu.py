@@ -358,3 +358,39 @@ def test_drop_in_refuses_host_tensors_without_the_test_double():
         gsr_densify.densify_and_prune(mdl, args["max_grad"], args["min_opacity"], args["extent"], 20)
     with pytest.raises(RuntimeError, match="CUDA tensors only"):
         gsr_densify.add_densification_stats(mdl, torch.zeros(mdl._xyz.shape[0], 3), torch.ones(mdl._xyz.shape[0], dtype=torch.int32))
+
+
+def test_training_loop_harness_runs_on_the_fused_densification(abi, monkeypatch):
+    """tools/c3_trainer.py with fused_densify = gsr_densify (the b200 arm of tools/train_c3.py), on the CPU through the test
+    double: the loop's densify events and statistics go through the library calls and leave a consistent model that
+    grows like the torch arm's (not bit-equal across arms: the 2-element norm differs in the last bit, which moves
+    the quantile threshold the harness derives from the statistics)."""
+    import torch
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import c3_trainer as T
+    import gsr_densify
+    import gsr_optim
+    from test_c3_trainer_cpu import FakeRasterizerModule, _loss, _setup
+    monkeypatch.setattr(gsr_densify, "_C", _EmulatedExtension(abi))
+    sizes = {}
+    for arm, fused in (("torch", None), ("fused", gsr_densify)):
+        cam, g = _setup(300)
+        g.fused_densify = fused
+        extent = float(torch.exp(g.scaling.detach()).max(dim=1).values.median()) / T.OptArgs.percent_dense
+        events = []
+        T.train(g, [cam], [torch.zeros(3 * 8 * 8)], FakeRasterizerModule, _loss, iterations=31, densify_from=5, densify_every=10,
+                target_P=700, extent=extent, bg=torch.zeros(3), timed=False, on_densify=lambda it, p0, p1, thr, st: events.append((it, p0, p1, st)))
+        assert [e[0] for e in events] == [10, 20, 30]
+        P = g.P
+        sizes[arm] = P
+        for n, w in zip(T.GROUPS, [(3,), (1, 3), (15, 3), (1,), (3,), (4,)]):
+            p = getattr(g, n)
+            assert p.shape == (P,) + w and p.requires_grad and isinstance(p, torch.nn.Parameter) and torch.isfinite(p).all()
+            grp = [x for x in g.optimizer.param_groups if x["name"] == n][0]
+            assert grp["params"][0] is p
+            st = g.optimizer.state[p]
+            assert st["exp_avg"].shape == p.shape and st["exp_avg_sq"].shape == p.shape
+        assert len(g.optimizer.state) == 6
+        assert g.xyz_gradient_accum.shape == (P, 1) and g.denom.shape == (P, 1) and g.max_radii2D.shape == (P,)
+        assert sum(st[0] for *_, st in events) > 0 and sum(st[1] for *_, st in events) > 0
+    assert abs(sizes["fused"] - sizes["torch"]) <= 0.02 * sizes["torch"], sizes

@@ -306,3 +306,144 @@ def test_fused_render_is_a_drop_in_for_the_reference_render():
     Pipe.convert_SHs_python = True                             # the python SH route (gsr_sh.eval_sh) gives the same picture
     py_sh = gsr_render.render(View, pc, Pipe, bg)
     assert float((py_sh["render"] - plain["render"]).abs().max()) <= 2e-5
+
+
+# ------------------------------------------------------------------------------------------------ densification (row 2, second half)
+DGOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_densify_cpu.npz")
+ATTR = {"xyz": "_xyz", "f_dc": "_features_dc", "f_rest": "_features_rest", "opacity": "_opacity", "scaling": "_scaling", "rotation": "_rotation"}
+
+
+class _DModel:
+    percent_dense = 0.01
+
+
+def _dmodel(tensors, moments, accum, denom, max_radii, percent_dense, opt_cls):
+    m = _DModel()
+    for n in NAMES:
+        setattr(m, ATTR[n], torch.nn.Parameter(torch.as_tensor(tensors[n], device="cuda").clone().contiguous()))
+    m.percent_dense = percent_dense
+    m.optimizer = opt_cls([{"params": [getattr(m, ATTR[n])], "lr": 1e-3, "name": n} for n in NAMES], lr=0.0, eps=1e-15)
+    if moments is not None:
+        for n in NAMES:
+            m.optimizer.state[getattr(m, ATTR[n])] = {"step": torch.tensor(2.0), "exp_avg": torch.as_tensor(moments[0][n], device="cuda").clone(),
+                                                      "exp_avg_sq": torch.as_tensor(moments[1][n], device="cuda").clone()}
+    m.xyz_gradient_accum = torch.as_tensor(accum, device="cuda").reshape(-1, 1).clone()
+    m.denom = torch.as_tensor(denom, device="cuda").reshape(-1, 1).clone()
+    m.max_radii2D = torch.as_tensor(max_radii, device="cuda").reshape(-1).clone()
+    return m
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c"])
+def test_densify_and_prune_reproduces_the_reference_models_fixture(tag, monkeypatch):
+    """The reference's GaussianModel.densify_and_prune, run by tests/golden/make_golden_densify.py, against the kernels:
+    the fixture's recorded samples are injected in place of the random draw; selections, order, copied rows and moments
+    exact, computed children (xyz, scaling) to 2e-6."""
+    import gsr_densify
+    z = np.load(DGOLD)
+    g = lambda k: z[f"{tag}_{k}"]
+    has = bool(g("with_moments"))
+    before = {n: g("before_p_" + n) for n in NAMES}
+    mom = ({n: g("before_m_" + n) for n in NAMES}, {n: g("before_v_" + n) for n in NAMES}) if has else None
+    m = _dmodel(before, mom, g("before_accum"), g("before_denom"), g("before_max_radii2D"), float(g("percent_dense")), torch.optim.Adam)
+    samples = torch.tensor(g("samples"), device="cuda")
+    monkeypatch.setattr(gsr_densify.torch, "normal", lambda mean, std, generator=None: samples)
+    launches0 = _launches()
+    P0, P1, n_clone, n_split = gsr_densify.densify_and_prune(m, float(g("max_grad")), float(g("min_opacity")), float(g("extent")),
+                                                             float(g("max_screen_size")) or None)
+    assert _launches() - launches0 == 3                        # classify, scan, apply
+    assert P1 == g("after_p_xyz").shape[0] and 2 * n_split == samples.shape[0]
+    for n in NAMES:
+        p = getattr(m, ATTR[n])
+        got, want = p.detach().cpu().numpy(), g("after_p_" + n)
+        assert got.shape == want.shape
+        if n in ("xyz", "scaling"):
+            np.testing.assert_allclose(got, want, rtol=2e-6, atol=2e-6)
+        else:
+            assert np.array_equal(got, want), n
+        if has:
+            st = m.optimizer.state[p]
+            assert np.array_equal(st["exp_avg"].cpu().numpy(), g("after_m_" + n)) and np.array_equal(st["exp_avg_sq"].cpu().numpy(), g("after_v_" + n))
+    assert m.xyz_gradient_accum.shape == (P1, 1) and not m.xyz_gradient_accum.any() and not m.denom.any() and not m.max_radii2D.any()
+
+
+def _torch_reference_arm():
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import c3_trainer as T
+    return T
+
+
+@pytest.mark.parametrize("P,screen", [(100_000, 20), (333_333, None)])
+def test_densify_and_prune_equals_the_torch_sequence_on_the_gpu_with_the_same_seed(P, screen):
+    """Same seed, same torch.normal call: the three-round torch sequence (tools/c3_trainer.py, the restatement of
+    scene/gaussian_model.py:366-597 used as the reference arm of the C3 harness) and the two library calls must give the
+    same model -- every tensor and both moments of every group, same row order."""
+    import gsr_densify
+    import gsr_optim
+    from helpers import S
+    T = _torch_reference_arm()
+    cam = S.make_camera(64, 64)
+    scene = S.make_scene(P, cam, sh_degree=3, seed=3)
+    arms = {}
+    for arm, fused in (("torch", None), ("fused", gsr_densify)):
+        g = T.Gaussians(scene, "cuda", torch.optim.Adam, gsr_optim.get_expon_lr_func, fused_densify=fused)
+        gen = torch.Generator(device="cuda").manual_seed(5)
+        for n in T.GROUPS:                                     # populate the moments
+            getattr(g, n).grad = torch.randn(getattr(g, n).shape, device="cuda", generator=gen) * 1e-3
+        g.optimizer.step()
+        g.denom = (torch.randint(1, 40, (P, 1), device="cuda", generator=gen).float() * (torch.rand(P, 1, device="cuda", generator=gen) > 0.15))
+        g.xyz_gradient_accum = torch.rand(P, 1, device="cuda", generator=gen) * 6e-4 * g.denom
+        extent = float(torch.exp(g.scaling.detach()).max(dim=1).values.median()) / T.OptArgs.percent_dense
+        torch.manual_seed(77)
+        g.densify_and_prune(0.0002, 0.005, extent, screen)
+        arms[arm] = g
+    a, b = arms["torch"], arms["fused"]
+    assert a.P == b.P and a.P != P
+    for n in T.GROUPS:
+        pa, pb = getattr(a, n).detach(), getattr(b, n).detach()
+        if n in ("xyz", "scaling"):
+            assert torch.allclose(pa, pb, rtol=2e-6, atol=2e-6), n
+            assert float((pa != pb).float().mean()) < 0.6          # the copied rows are identical
+        else:
+            assert torch.equal(pa, pb), n
+        sa, sb = a.optimizer.state[getattr(a, n)], b.optimizer.state[getattr(b, n)]
+        assert torch.equal(sa["exp_avg"], sb["exp_avg"]) and torch.equal(sa["exp_avg_sq"], sb["exp_avg_sq"]), n
+    assert torch.equal(a.denom, b.denom) and torch.equal(a.max_radii2D, b.max_radii2D)
+
+
+def test_densification_statistics_kernel_against_torch_and_the_fixture():
+    import gsr_densify
+    z = np.load(DGOLD)
+    s = lambda k: z["stats_" + k]
+    m = _DModel()
+    m.xyz_gradient_accum, m.denom = torch.tensor(s("accum0"), device="cuda"), torch.tensor(s("denom0"), device="cuda")
+    m.max_radii2D = torch.tensor(s("max_radii0"), device="cuda")
+    vsp = torch.zeros(s("vs_grad").shape, device="cuda", requires_grad=True)
+    vsp.grad = torch.tensor(s("vs_grad"), device="cuda")
+    launches0 = _launches()
+    gsr_densify.add_densification_stats(m, vsp, torch.tensor(s("radii"), device="cuda"))
+    assert _launches() - launches0 == 1
+    assert np.array_equal(m.denom.cpu().numpy(), s("denom1")) and np.array_equal(m.max_radii2D.cpu().numpy(), s("max_radii1"))
+    np.testing.assert_allclose(m.xyz_gradient_accum.cpu().numpy(), s("accum1"), rtol=2e-7, atol=0)
+    # a large model against the torch statements of train.py:153-158 on the GPU
+    P = 1_000_003
+    gen = torch.Generator(device="cuda").manual_seed(1)
+    accum, denom = torch.rand(P, 1, device="cuda", generator=gen), torch.randint(0, 9, (P, 1), device="cuda", generator=gen).float()
+    mr = torch.rand(P, device="cuda", generator=gen) * 30
+    radii = (torch.randint(-2, 60, (P,), device="cuda", generator=gen) * (torch.rand(P, device="cuda", generator=gen) > 0.3)).int()
+    grad = torch.randn(P, 3, device="cuda", generator=gen) * 1e-3
+    m.xyz_gradient_accum, m.denom, m.max_radii2D = accum.clone(), denom.clone(), mr.clone()
+    gsr_densify.add_densification_stats(m, grad, radii)
+    vis = radii > 0
+    mr[vis] = torch.max(mr[vis], radii[vis].float())
+    accum[vis] += torch.norm(grad[vis, :2], dim=-1, keepdim=True)
+    denom[vis] += 1
+    assert torch.equal(m.denom, denom) and torch.equal(m.max_radii2D, mr)
+    assert torch.allclose(m.xyz_gradient_accum, accum, rtol=2e-7, atol=0)
+
+
+def test_densify_rejects_host_tensors():
+    import gsr_densify
+    m = _DModel()
+    with pytest.raises(RuntimeError, match="CUDA tensors only"):
+        from diff_gaussian_rasterization import _C
+        _C.densify_stats(torch.zeros(4, 3), torch.ones(4, dtype=torch.int32), torch.zeros(4), torch.zeros(4), None)

@@ -58,7 +58,8 @@ GROUPS = ("xyz", "f_dc", "f_rest", "opacity", "scaling", "rotation")
 class Gaussians:
     """The six raw parameter tensors + the densification bookkeeping of GaussianModel, nothing else."""
 
-    def __init__(self, scene, device, optimizer_cls, lr_func, opt=OptArgs, spatial_lr_scale=1.0):
+    def __init__(self, scene, device, optimizer_cls, lr_func, opt=OptArgs, spatial_lr_scale=1.0, fused_densify=None):
+        self.fused_densify = fused_densify          # the gsr_densify module (b200 arm) or None (torch ops, as the reference)
         t = lambda a: torch.as_tensor(a, dtype=torch.float32, device=device)
         shs = t(scene["shs"])
         self.xyz = torch.nn.Parameter(t(scene["means3D"]).contiguous())
@@ -85,6 +86,15 @@ class Gaussians:
         self.optimizer = optimizer_cls(groups, lr=0.0, eps=1e-15)
         self.xyz_lr = lr_func(lr_init=opt.position_lr_init * spatial_lr_scale, lr_final=opt.position_lr_final * spatial_lr_scale,
                               lr_delay_mult=opt.position_lr_delay_mult, max_steps=opt.position_lr_max_steps)
+
+    # the reference's attribute names (scene/gaussian_model.py:47-57), which gsr_densify reads and writes
+    _xyz = property(lambda s: s.xyz, lambda s, v: setattr(s, "xyz", v))
+    _features_dc = property(lambda s: s.f_dc, lambda s, v: setattr(s, "f_dc", v))
+    _features_rest = property(lambda s: s.f_rest, lambda s, v: setattr(s, "f_rest", v))
+    _opacity = property(lambda s: s.opacity, lambda s, v: setattr(s, "opacity", v))
+    _scaling = property(lambda s: s.scaling, lambda s, v: setattr(s, "scaling", v))
+    _rotation = property(lambda s: s.rotation, lambda s, v: setattr(s, "rotation", v))
+    percent_dense = property(lambda s: s.opt.percent_dense)
 
     # activations, scene/gaussian_model.py:114-138
     @property
@@ -165,6 +175,10 @@ class Gaussians:
         return n_sel
 
     def densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size, generator=None):   # :558-597
+        if self.fused_densify is not None:
+            P0, P1, n_clone_kept, n_split = self.fused_densify.densify_and_prune(self, max_grad, min_opacity, extent, max_screen_size,
+                                                                                 generator=generator)
+            return n_clone_kept, n_split, None
         grads = self.xyz_gradient_accum / self.denom
         grads[grads.isnan()] = 0.0
         n_clone = self.densify_and_clone(grads, max_grad, extent)
@@ -259,8 +273,11 @@ def train(g, cams, targets, rasterizer_module, loss_fn, iterations, densify_from
         ph.mark()
         with torch.no_grad():
             vis, radii = pkg["visibility_filter"], pkg["radii"]
-            g.max_radii2D[vis] = torch.max(g.max_radii2D[vis], radii[vis].to(g.max_radii2D.dtype))
-            g.add_densification_stats(pkg["viewspace_points"], vis)
+            if g.fused_densify is not None:
+                g.fused_densify.add_densification_stats(g, pkg["viewspace_points"], radii)
+            else:
+                g.max_radii2D[vis] = torch.max(g.max_radii2D[vis], radii[vis].to(g.max_radii2D.dtype))
+                g.add_densification_stats(pkg["viewspace_points"], vis)
             P_before = g.P
             if iteration > densify_from and iteration % densify_every == 0 and iteration < iterations:
                 event += 1

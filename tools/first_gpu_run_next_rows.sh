@@ -6,9 +6,9 @@ set -u
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests -m gpu -q -rxX -k "not zz_next" 2>&1 | tail -5 | tee gpurun_out/r02_pytest_gpu_established.log
 timeout 600 python -m pytest tests/test_zz_next_rows_gpu.py -m gpu -q -rxX 2>&1 | tail -40 | tee gpurun_out/r02_pytest_gpu_next_rows.log
-timeout 120 compute-sanitizer --tool memcheck python -m pytest tests/test_zz_next_rows_gpu.py -m gpu -q -x -k "1000 or 257 or 777 or 129" > gpurun_out/r02_memcheck_next_rows.log 2>&1; echo "memcheck rc=$?"; tail -3 gpurun_out/r02_memcheck_next_rows.log
+timeout 120 compute-sanitizer --tool memcheck python -m pytest tests/test_zz_next_rows_gpu.py -m gpu -q -x -k "1000 or 257 or 777 or 129 or fixture" > gpurun_out/r02_memcheck_next_rows.log 2>&1; echo "memcheck rc=$?"; tail -3 gpurun_out/r02_memcheck_next_rows.log
 python tests/golden/make_golden_knn_gpu.py > gpurun_out/r02_make_golden_knn.log 2>&1; echo "knn golden rc=$?"
-timeout 300 python tools/bench_next.py all > gpurun_out/r02_bench_next.jsonl 2> gpurun_out/r02_bench_next.err; echo "bench_next rc=$?"; cat gpurun_out/r02_bench_next.jsonl | cut -c1-400
+timeout 420 python tools/bench_next.py all > gpurun_out/r02_bench_next.jsonl 2> gpurun_out/r02_bench_next.err; echo "bench_next rc=$?"; cat gpurun_out/r02_bench_next.jsonl | cut -c1-400
 timeout 300 python tools/train_c3.py --impl b200 > gpurun_out/r02_c3_b200.json 2> gpurun_out/r02_c3_b200.err; echo "c3 b200 rc=$?"
 timeout 400 python tools/train_c3.py --impl reference > gpurun_out/r02_c3_reference.json 2> gpurun_out/r02_c3_reference.err; echo "c3 reference rc=$?"
 python - <<'PY'
@@ -21,7 +21,7 @@ for impl in ("b200", "reference"):
         print(impl, "no result:", e)
 PY
 timeout 200 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/r02_launches_next.csv python tools/bench_next.py all --steps 2 --warmup 1 > gpurun_out/r02_ncu_next.log 2>&1; echo "ncu list rc=$?"
-timeout 300 ncu --set full --clock-control none --import-source on -k regex:"adam_kernel|knn_search_kernel|knn_gather_kernel" -c 6 -o /tmp/prof_next -f python tools/bench_next.py all --steps 1 --warmup 1 > gpurun_out/r02_ncu_full_next.log 2>&1; echo "ncu full rc=$?"
+timeout 300 ncu --set full --clock-control none --import-source on -k regex:"adam_kernel|knn_search_kernel|knn_gather_kernel|densify_apply_kernel|densify_classify_kernel" -c 8 -o /tmp/prof_next -f python tools/bench_next.py all --steps 1 --warmup 1 > gpurun_out/r02_ncu_full_next.log 2>&1; echo "ncu full rc=$?"
 ncu -i /tmp/prof_next.ncu-rep --page raw --csv > gpurun_out/r02_prof_next_raw.csv 2>/dev/null
 python tools/ncu_summary.py gpurun_out/r02_prof_next_raw.csv > gpurun_out/r02_ncu_next_summary.txt 2>/dev/null
 ls -la gpurun_out | head -30

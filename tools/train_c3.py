@@ -84,16 +84,17 @@ def main():
     scene = S.make_scene(a.P0, base, sh_degree=3, seed=0)
     if a.impl == "b200":
         import loss_utils
-        module, opt_cls = mine, gsr_optim.FusedAdam
+        import gsr_densify
+        module, opt_cls, fused_densify = mine, gsr_optim.FusedAdam, gsr_densify
         loss_fn = lambda img, gt, lam: loss_utils.fused_l1_ssim_loss(img, gt, lam)[0]
     else:
         import helpers
         import loss_ref
         assert helpers.have_ref(), "oracle/_ref is missing: build it in the container (python oracle/build_ref.py)"
-        module, opt_cls = helpers.ref_module(), torch.optim.Adam
+        module, opt_cls, fused_densify = helpers.ref_module(), torch.optim.Adam, None
         w1 = loss_ref.window_1d().cuda()
         loss_fn = torch_loss((w1.unsqueeze(1) @ w1.unsqueeze(0)).expand(3, 1, 11, 11).contiguous())
-    g = T.Gaussians(scene, "cuda", opt_cls, gsr_optim.get_expon_lr_func)
+    g = T.Gaussians(scene, "cuda", opt_cls, gsr_optim.get_expon_lr_func, fused_densify=fused_densify)
     # clone vs split is decided by max scale against percent_dense * extent (scene/gaussian_model.py:512,545): put the
     # boundary at the median so both branches run
     extent = float(torch.exp(g.scaling.detach()).max(dim=1).values.median()) / T.OptArgs.percent_dense
