@@ -160,7 +160,10 @@ GSR_DI void split_child_xyz(const float* rot, const float* xyz, const float* smp
 
 // Moves the block's rows of one tensor group.  s_dst[c][row]: destination row for category c (0 original, 1 clone,
 // 2 first child; further children follow at a stride of n_chk rows), or -1.  Thread t takes floats t, t + NT, ... of the
-// block's nrows * w contiguous floats; row and column advance without a division per element.
+// block's nrows * w contiguous floats; row and column advance without a division per element.  Four elements are in
+// flight per thread (up to twelve loads issued before the first store): the kernel is a gather-free copy whose only
+// limit should be HBM, and one load per thread at a time does not cover the memory latency.
+constexpr int DENSIFY_UNROLL = 4;
 template <int NT>
 GSR_DI void densify_move_rows(const DensifyGroupDev& G, size_t first_row, int nrows, const int (*s_dst)[DENSIFY_THREADS], int copies, int n_chk,
                               bool children_computed, int t) {
@@ -168,31 +171,44 @@ GSR_DI void densify_move_rows(const DensifyGroupDev& G, size_t first_row, int nr
     const size_t src0 = first_row * (size_t)w;
     const int n = nrows * w;
     const int qstep = NT / w, rstep = NT % w;
+    const bool state = G.mo != nullptr;
     int row = t / w, col = t - row * w;
-    for (int f = t; f < n; f += NT) {
-        const int d_ok = s_dst[0][row], d_ck = s_dst[1][row], d_ch = s_dst[2][row];
-        if ((d_ok & d_ck & d_ch) >= 0) {                              // at least one destination (not all -1)
-            const float val = __ldg(G.p + src0 + f);
-            if (d_ok >= 0) {
-                const size_t d = (size_t)d_ok * w + col;
-                G.po[d] = val;
-                if (G.mo) { G.mo[d] = __ldg(G.m + src0 + f); G.vo[d] = __ldg(G.v + src0 + f); }
+    for (int f0 = t; f0 < n; f0 += NT * DENSIFY_UNROLL) {
+        int d_ok[DENSIFY_UNROLL], d_ck[DENSIFY_UNROLL], d_ch[DENSIFY_UNROLL], cl[DENSIFY_UNROLL];
+        float val[DENSIFY_UNROLL], mv[DENSIFY_UNROLL], vv[DENSIFY_UNROLL];
+#pragma unroll
+        for (int u = 0; u < DENSIFY_UNROLL; u++) {
+            const int f = f0 + u * NT;
+            d_ok[u] = d_ck[u] = d_ch[u] = -1;
+            cl[u] = col;
+            if (f < n) {
+                d_ok[u] = s_dst[0][row]; d_ck[u] = s_dst[1][row]; d_ch[u] = s_dst[2][row];
+                if ((d_ok[u] & d_ck[u] & d_ch[u]) >= 0) val[u] = __ldg(G.p + src0 + f);           // at least one destination (not all -1)
+                if (state && d_ok[u] >= 0) { mv[u] = __ldg(G.m + src0 + f); vv[u] = __ldg(G.v + src0 + f); }
             }
-            if (d_ck >= 0) {
-                const size_t d = (size_t)d_ck * w + col;
-                G.po[d] = val;
-                if (G.mo) { G.mo[d] = 0.f; G.vo[d] = 0.f; }
+            row += qstep; col += rstep;
+            if (col >= w) { col -= w; row++; }
+        }
+#pragma unroll
+        for (int u = 0; u < DENSIFY_UNROLL; u++) {
+            if (d_ok[u] >= 0) {
+                const size_t d = (size_t)d_ok[u] * w + cl[u];
+                G.po[d] = val[u];
+                if (state) { G.mo[d] = mv[u]; G.vo[d] = vv[u]; }
             }
-            if (d_ch >= 0) {
+            if (d_ck[u] >= 0) {
+                const size_t d = (size_t)d_ck[u] * w + cl[u];
+                G.po[d] = val[u];
+                if (state) { G.mo[d] = 0.f; G.vo[d] = 0.f; }
+            }
+            if (d_ch[u] >= 0) {
                 for (int k = 0; k < copies; k++) {
-                    const size_t d = ((size_t)d_ch + (size_t)k * n_chk) * w + col;
-                    if (!children_computed) G.po[d] = val;
-                    if (G.mo) { G.mo[d] = 0.f; G.vo[d] = 0.f; }
+                    const size_t d = ((size_t)d_ch[u] + (size_t)k * n_chk) * w + cl[u];
+                    if (!children_computed) G.po[d] = val[u];
+                    if (state) { G.mo[d] = 0.f; G.vo[d] = 0.f; }
                 }
             }
         }
-        row += qstep; col += rstep;
-        if (col >= w) { col -= w; row++; }
     }
 }
 
