@@ -1,4 +1,4 @@
-# The host-emulated kernel and ABI tests (tests/test_kernels_emulated.py, tests/test_abi_emulated.py) under a sanitizer:
+# The host-emulated kernel and ABI tests (tests/test_kernels_emulated.py, tests/test_abi_emulated.py, tests/test_densify_cpu.py) under a sanitizer:
 #   bash tools/emu_sanitize.sh address   out-of-bounds reads / writes of the kernels on host arrays (numpy's buffers get
 #                                        red zones through the preloaded runtime) -- the host stand-in for memcheck
 #   bash tools/emu_sanitize.sh thread    data races between the emulated threads of a block, i.e. a missing
@@ -22,6 +22,6 @@ if [ "$KIND" = address ]; then
 else
   export LD_PRELOAD=$(gcc -print-file-name=libtsan.so) TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 exitcode=0"
 fi
-GSR_EMU_SO_DIR=$D GSR_EMU_ABI_SO=$D/libemu_abi.so python -m pytest tests/test_kernels_emulated.py tests/test_abi_emulated.py -q -p no:cacheprovider > $D/run.log 2>&1 || true
+GSR_EMU_SO_DIR=$D GSR_EMU_ABI_SO=$D/libemu_abi.so python -m pytest tests/test_kernels_emulated.py tests/test_abi_emulated.py tests/test_densify_cpu.py -q -p no:cacheprovider > $D/run.log 2>&1 || true
 tail -3 $D/run.log
 echo "sanitizer reports: $(grep -c -E 'ERROR: AddressSanitizer|WARNING: ThreadSanitizer' $D/run.log || true)"
