@@ -349,6 +349,8 @@ def test_drop_in_statistics_update_matches_the_reference(abi, monkeypatch):
     np.testing.assert_allclose(mdl.xyz_gradient_accum.numpy(), s("accum1"), rtol=2e-7, atol=0)
 
 
+@pytest.mark.skipif(bool(os.environ.get("GSR_EMU_ABI_SO")), reason="sanitizer run (tools/emu_sanitize.sh): the real torch extension is not "
+                    "instrumented and throws through the preloaded runtime")
 def test_drop_in_refuses_host_tensors_without_the_test_double():
     """The real extension has no CPU path: host tensors are rejected, nothing is computed."""
     import torch
