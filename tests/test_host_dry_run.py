@@ -1,0 +1,31 @@
+"""The Python side of the `first_gpu_run` GPU tests, run on the host (tools/host_dry_run_gpu_tests.py): the package's Python
+API and a host build of the product's own torch binding over the host-emulated C ABI.  By default a subset that finishes
+in about a minute (the densification fixtures through gsr_densify and the binding, the unaligned / masked Adam step);
+GSR_SLOW=1 runs all 25 invocations (about ten minutes).  Keeps typos in GPU-only tests from costing GPU minutes."""
+import os
+import subprocess
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TOOL = os.path.join(ROOT, "tools", "host_dry_run_gpu_tests.py")
+
+
+def _run(only, expect):
+    r = subprocess.run([sys.executable, TOOL, "5000", only], capture_output=True, text=True, timeout=3000)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "dry run complete: %d test invocations" % expect in r.stdout, r.stdout[-2000:]
+
+
+def test_densification_gpu_tests_python_side_runs_on_the_host():
+    _run("fixture", 4)          # three reference-model fixtures + the statistics kernel test
+
+
+def test_adam_gpu_test_with_unaligned_views_and_mask_runs_on_the_host():
+    _run("unaligned", 1)
+
+
+@pytest.mark.skipif(os.environ.get("GSR_SLOW") != "1", reason="all 25 invocations take about ten minutes: set GSR_SLOW=1 (green when written)")
+def test_every_first_gpu_run_test_covered_by_the_dry_run():
+    _run("", 25)

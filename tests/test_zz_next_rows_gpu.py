@@ -266,7 +266,10 @@ def test_fused_render_is_a_drop_in_for_the_reference_render():
         max_sh_degree = 3
         _xyz, _features_dc, _features_rest = raw["xyz"], raw["f_dc"], raw["f_rest"]
         _opacity, _scaling, _rotation = raw["opacity"], raw["scaling"], raw["rotation"]
-        scaling_activation, opacity_activation, rotation_activation = torch.exp, torch.sigmoid, torch.nn.functional.normalize
+
+        def __init__(self):      # instance attributes, as GaussianModel.setup_functions sets them (a class attribute would bind)
+            self.scaling_activation, self.opacity_activation, self.rotation_activation = torch.exp, torch.sigmoid, torch.nn.functional.normalize
+
         get_xyz = property(lambda s: s._xyz)
         get_scaling = property(lambda s: s.scaling_activation(s._scaling))
         get_rotation = property(lambda s: s.rotation_activation(s._rotation))
@@ -287,6 +290,7 @@ def test_fused_render_is_a_drop_in_for_the_reference_render():
 
     bg = torch.tensor([0.0, 0.0, 0.0], device="cuda")
     pc = PC()
+    assert gsr_render._default_activations(pc)                # so this call takes the fused route (raw tensors into the kernels)
     fused = gsr_render.render(View, pc, Pipe, bg)
     assert set(fused) == {"render", "viewspace_points", "visibility_filter", "radii"}
     fused["render"].sum().backward()
@@ -295,6 +299,7 @@ def test_fused_render_is_a_drop_in_for_the_reference_render():
     for v in raw.values():
         v.grad = None
     pc.scaling_activation = lambda x: torch.exp(x)            # not the default object: render() takes the reference's route
+    assert not gsr_render._default_activations(pc)
     plain = gsr_render.render(View, pc, Pipe, bg)
     plain["render"].sum().backward()
     assert float((fused["render"] - plain["render"]).abs().max()) <= 1e-5
