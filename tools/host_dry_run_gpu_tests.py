@@ -11,6 +11,7 @@ product's own kernel sources run by emu.h).  So the Python API, the binding's te
 orchestration and the kernels' logic all run; what does not run is the hardware.  Tests whose point is a device check
 (host tensors must be rejected) or a size that the emulation cannot finish in minutes are left out.
 
+    python tools/host_dry_run_gpu_tests.py --scripts      (bench_next.py and train_c3.py --impl b200 at toy sizes)
     python tools/host_dry_run_gpu_tests.py [P of the torch-sequence comparison, default 20000] [substring of the test names to run]
 """
 import ctypes as C
@@ -104,5 +105,43 @@ def main():
           "(the kernels themselves still need the B200)" % count[0])
 
 
+def dry_run_scripts():
+    """The measurement scripts of round 2's first GPU call (tools/first_gpu_run_next_rows.sh) at toy sizes: bench_next.py (Adam,
+    distCUDA2, densification) and the b200 arm of train_c3.py (render -> fused loss -> backward -> statistics -> densify ->
+    FusedAdam, for a few iterations).  The printed numbers mean nothing; the point is that every line of them executes."""
+    import importlib.util
+    import time
+    import build_emu
+    import c3_trainer  # noqa: F401
+    spec = importlib.util.spec_from_file_location("_C_host", build_emu.build_binding())
+    host = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(host)
+    sys.modules["diff_gaussian_rasterization._C"] = host
+    install_device_shim()
+
+    class HostEvent:
+        def __init__(self, enable_timing=False): self.t = 0.0
+        def record(self, stream=None): self.t = time.time()
+        def elapsed_time(self, other): return (other.t - self.t) * 1e3
+        def synchronize(self): pass
+    torch.cuda.Event = HostEvent
+    torch.cuda.synchronize = lambda *a, **k: None
+    torch.cuda.is_available = lambda: True
+    torch.cuda.is_current_stream_capturing = lambda: False
+    sys.modules["torch.cuda.graphs"].is_current_stream_capturing = lambda: False
+
+    import bench_next
+    bench_next.ref_knn_module = lambda: None                      # the reference's simple-knn build is CUDA only
+    sys.argv = ["bench_next.py", "all", "--P", "3000", "--steps", "2", "--warmup", "1"]
+    bench_next.main()
+    print("ok  bench_next.py all", flush=True)
+    import train_c3
+    sys.argv = ["train_c3.py", "--impl", "b200", "--P0", "400", "--target", "900", "--iterations", "25", "--densify-from", "5",
+                "--densify-every", "10", "--width", "64", "--height", "48", "--views", "2"]
+    train_c3.main()
+    print("ok  train_c3.py --impl b200", flush=True)
+    print("script dry run complete")
+
+
 if __name__ == "__main__":
-    main()
+    dry_run_scripts() if "--scripts" in sys.argv else main()
