@@ -29,3 +29,11 @@ def test_adam_gpu_test_with_unaligned_views_and_mask_runs_on_the_host():
 @pytest.mark.skipif(os.environ.get("GSR_SLOW") != "1", reason="all 25 invocations take about ten minutes: set GSR_SLOW=1 (green when written)")
 def test_every_first_gpu_run_test_covered_by_the_dry_run():
     _run("", 25)
+
+
+def test_graft_entry_smoke_runs_on_the_host_and_matches_the_oracle():
+    """__graft_entry__.smoke() -- the driver's round-end check on cuda:0 -- through the host binding: same Python, same
+    binding source, same kernels' logic; sorted lists, ranges, radii, image and gradients against the oracle."""
+    r = subprocess.run([sys.executable, TOOL, "--scripts", "--smoke"], capture_output=True, text=True, timeout=1500)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+    assert "smoke ok" in r.stdout and "ok  __graft_entry__.smoke()" in r.stdout

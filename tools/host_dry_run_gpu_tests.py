@@ -11,6 +11,7 @@ product's own kernel sources run by emu.h).  So the Python API, the binding's te
 orchestration and the kernels' logic all run; what does not run is the hardware.  Tests whose point is a device check
 (host tensors must be rejected) or a size that the emulation cannot finish in minutes are left out.
 
+    python tools/host_dry_run_gpu_tests.py --scripts --smoke   (__graft_entry__.smoke() only, one minute)
     python tools/host_dry_run_gpu_tests.py --scripts      (bench_next.py and train_c3.py --impl b200 at toy sizes)
     python tools/host_dry_run_gpu_tests.py [P of the torch-sequence comparison, default 20000] [substring of the test names to run]
 """
@@ -130,6 +131,11 @@ def dry_run_scripts():
     torch.cuda.is_current_stream_capturing = lambda: False
     sys.modules["torch.cuda.graphs"].is_current_stream_capturing = lambda: False
 
+    if "--smoke" in sys.argv:
+        import __graft_entry__
+        __graft_entry__.smoke()                                    # the driver's round-end smoke test, same code path
+        print("ok  __graft_entry__.smoke()", flush=True)
+        return
     import bench_next
     bench_next.ref_knn_module = lambda: None                      # the reference's simple-knn build is CUDA only
     sys.argv = ["bench_next.py", "all", "--P", "3000", "--steps", "2", "--warmup", "1"]
