@@ -1,6 +1,7 @@
 """The Python side of the `first_gpu_run` GPU tests, run on the host (tools/host_dry_run_gpu_tests.py): the package's Python
 API and a host build of the product's own torch binding over the host-emulated C ABI.  By default a subset that finishes
-in about a minute (the densification fixtures through gsr_densify and the binding, the unaligned / masked Adam step);
+in about two minutes (the densification fixtures through gsr_densify and the binding, the unaligned / masked Adam step,
+__graft_entry__.smoke());
 GSR_SLOW=1 runs all 25 invocations (about ten minutes).  Keeps typos in GPU-only tests from costing GPU minutes."""
 import os
 import subprocess
@@ -19,7 +20,7 @@ def _run(only, expect):
 
 
 def test_densification_gpu_tests_python_side_runs_on_the_host():
-    _run("fixture", 4)          # three reference-model fixtures + the statistics kernel test
+    _run("reference_models_fixture", 3)          # the three fixtures of the reference's own GaussianModel
 
 
 def test_adam_gpu_test_with_unaligned_views_and_mask_runs_on_the_host():
