@@ -2,7 +2,7 @@
 API and a host build of the product's own torch binding over the host-emulated C ABI.  By default a subset that finishes
 in about two minutes (the densification fixtures through gsr_densify and the binding, the unaligned / masked Adam step,
 __graft_entry__.smoke());
-GSR_SLOW=1 runs all 25 invocations (about ten minutes).  Keeps typos in GPU-only tests from costing GPU minutes."""
+GSR_SLOW=1 runs all 25 invocations (about fifteen minutes).  Keeps typos in GPU-only tests from costing GPU minutes."""
 import os
 import subprocess
 import sys
@@ -27,7 +27,7 @@ def test_adam_gpu_test_with_unaligned_views_and_mask_runs_on_the_host():
     _run("unaligned", 1)
 
 
-@pytest.mark.skipif(os.environ.get("GSR_SLOW") != "1", reason="all 25 invocations take about ten minutes: set GSR_SLOW=1 (green when written)")
+@pytest.mark.skipif(os.environ.get("GSR_SLOW") != "1", reason="all 25 invocations take about fifteen minutes: set GSR_SLOW=1 (green when written)")
 def test_every_first_gpu_run_test_covered_by_the_dry_run():
     _run("", 25)
 
