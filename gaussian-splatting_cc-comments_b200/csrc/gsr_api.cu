@@ -578,6 +578,7 @@ int gsr_view_buffers(int P, int R, int width, int height, const char* geom_buffe
     out->packed = reinterpret_cast<const float*>(geom.packed);
     out->tiles_touched = geom.tiles_touched;
     out->clamped = geom.clamped;
+    out->warp_mask = bin.warp_mask;
     return GSR_OK;
 }
 

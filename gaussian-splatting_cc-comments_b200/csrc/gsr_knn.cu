@@ -122,7 +122,10 @@ __global__ void __launch_bounds__(KNN_BOX) knn_gather_kernel(int P, const float*
 }
 
 // squared length of (dx, dy, dz), rounded as the point distances are: one product, two FMAs
-__device__ __forceinline__ float sq3(float dx, float dy, float dz) { return __fmaf_rn(dz, dz, __fmaf_rn(dy, dy, __fmul_rn(dx, dx))); }
+// The contraction of the reference's sm_100 binary (boxMeanDist: FMUL on the y difference, then FFMA x, then FFMA z --
+// nvcc evaluates d.x*d.x + d.y*d.y + d.z*d.z as fma(dz, dz, fma(dx, dx, dy*dy)); same order in distBoxPoint).  Pinned by the
+// fixture the reference build wrote on a B200 (tests/golden/ref_knn_cuda.npz).
+__device__ __forceinline__ float sq3(float dx, float dy, float dz) { return __fmaf_rn(dz, dz, __fmaf_rn(dx, dx, __fmul_rn(dy, dy))); }
 
 // updateKBest<3> (simple_knn.cu:136-150): keep the three smallest, ascending; min/max network == its compare-and-swap chain
 __device__ __forceinline__ void keep3(float d, float& b0, float& b1, float& b2) {

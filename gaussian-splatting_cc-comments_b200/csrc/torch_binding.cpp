@@ -301,7 +301,7 @@ std::vector<torch::Tensor> viewBuffers(int P, int R, int W, int H, const torch::
     };
     return {mk(v.point_list, {R}, torch::kInt32), mk(v.ranges, {tiles, 2}, torch::kInt32), mk(v.n_contrib, {H, W}, torch::kInt32),
             mk(v.final_T, {H, W}, torch::kFloat32), mk(v.packed, {P, 12}, torch::kFloat32), mk(v.tiles_touched, {P}, torch::kInt32),
-            mk(v.clamped, {P}, torch::kUInt8)};
+            mk(v.clamped, {P}, torch::kUInt8), mk(v.warp_mask, {R}, torch::kUInt8)};
 }
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {

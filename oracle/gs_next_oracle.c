@@ -11,11 +11,12 @@
  *                    the CPU for the reference's six groups and learning rates (generator: tests/golden/make_golden_adam.py,
  *                    which imports the reference's arguments.OptimizationParams and utils.general_utils.get_expon_lr_func).
  *                    tests/test_adam_cpu.py checks this function against them.
- *   gno_knn_mean_d2: the reference function needs a GPU (simple_knn.cu is CUDA only) and the reference ships no vectors
- *                    for it: PARITY UNPINNED against the reference binary this round.  Its result is defined exactly
- *                    (three smallest squared distances to other points, averaged), so it is checked against an
- *                    independent exact search (scipy cKDTree, float64) in tests/test_knn_cpu.py instead; a fixture from
- *                    the reference build is round 2's first GPU call (tests/golden/make_golden_knn_gpu.py).
+ *   gno_knn_mean_d2: the reference function needs a GPU (simple_knn.cu is CUDA only) and ships no vectors.  PINNED since
+ *                    round 2: tests/golden/ref_knn_cuda.npz was written on a B200 by the reference's own simple-knn built
+ *                    for sm_100 (oracle/build_ref.py: build_knn; generator tests/golden/make_golden_knn_gpu.py), and this
+ *                    function reproduces all six cases bit for bit (tests/test_knn_cpu.py).  The fixture is what showed
+ *                    that nvcc contracts d.x*d.x + d.y*d.y + d.z*d.z as fma(dz, dz, fma(dx, dx, dy*dy)).  Also checked
+ *                    against an independent exact search (scipy cKDTree, float64).
  */
 #include <float.h>
 #include <math.h>
@@ -83,13 +84,13 @@ static float dist_box_point(const minmax_t* box, const float* p) { /* simple_knn
     float diff[3] = {0.f, 0.f, 0.f};
     for (int a = 0; a < 3; a++)
         if (p[a] < box->mn[a] || p[a] > box->mx[a]) diff[a] = fminf(fabsf(p[a] - box->mn[a]), fabsf(p[a] - box->mx[a]));
-    return fmaf(diff[2], diff[2], fmaf(diff[1], diff[1], diff[0] * diff[0]));
+    return fmaf(diff[2], diff[2], fmaf(diff[0], diff[0], diff[1] * diff[1])); /* FMUL y, FFMA x, FFMA z in the reference's sm_100 SASS */
 }
 
 static void update_k_best(const float* ref, const float* point, float* knn) { /* updateKBest<3>, simple_knn.cu:136-150 */
     const float d[3] = {point[0] - ref[0], point[1] - ref[1], point[2] - ref[2]};
-    /* FMUL, FFMA, FFMA in the reference's sm_100 SASS */
-    float dist = fmaf(d[2], d[2], fmaf(d[1], d[1], d[0] * d[0]));
+    /* the reference's sm_100 SASS: FMUL on the y difference, then FFMA x, then FFMA z */
+    float dist = fmaf(d[2], d[2], fmaf(d[0], d[0], d[1] * d[1]));
     for (int j = 0; j < 3; j++) {
         if (knn[j] > dist) {
             const float t = knn[j];

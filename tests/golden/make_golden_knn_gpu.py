@@ -16,11 +16,11 @@ ROOT = os.path.dirname(os.path.dirname(HERE))
 
 
 def main():
-    so = os.path.join(ROOT, "oracle", "_ref", "simple_knn", "_C.so")
+    so = os.path.join(ROOT, "oracle", "_ref", "simple_knn", "ref_simple_knn_C.so")
     if not (os.path.exists(so) and torch.cuda.is_available()):
-        print("needs oracle/_ref/simple_knn/_C.so and a GPU")
+        print("needs oracle/_ref/simple_knn/ref_simple_knn_C.so and a GPU")
         return 1
-    spec = importlib.util.spec_from_file_location("_C", so)
+    spec = importlib.util.spec_from_file_location("ref_simple_knn_C", so)
     ref = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(ref)
     out = {}

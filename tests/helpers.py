@@ -111,12 +111,12 @@ def run_torch(mod, cam, scene, dL=None, bg=(0, 0, 0), use="sh", cov="sr", device
     if is_ref:
         out.update(slice_ref_buffers(P, R, cam["W"], cam["H"], geom, binning, img))
     else:
-        pl, rg, nc, ft, packed, tt, cl = mod._C.view_buffers(P, R, cam["W"], cam["H"], geom, binning, img)
+        pl, rg, nc, ft, packed, tt, cl, wm = mod._C.view_buffers(P, R, cam["W"], cam["H"], geom, binning, img)
         pk = packed.cpu().numpy()
         out.update(point_list=pl.cpu().numpy().view(np.uint32), ranges=rg.cpu().numpy().view(np.uint32),
                    n_contrib=nc.cpu().numpy().view(np.uint32), final_T=ft.cpu().numpy(), packed=pk,
                    means2D=pk[:, 0:2], conic_opacity=np.concatenate([pk[:, 2:5], pk[:, 6:7]], 1), rgb=pk[:, 7:10],
-                   tiles_touched=tt.cpu().numpy().view(np.uint32), clamped_bits=cl.cpu().numpy())
+                   tiles_touched=tt.cpu().numpy().view(np.uint32), clamped_bits=cl.cpu().numpy(), warp_mask=wm.cpu().numpy())
     if dL is not None:
         color.backward(t(dL))
         out["grads"] = {k: (ins[k].grad.detach().cpu().numpy() if k in ins and ins[k].grad is not None else None)

@@ -90,7 +90,7 @@ def _forward(lib, z, D, smod=1.0, raw=None, split=False, shs=None):
 
 
 class BufferView(C.Structure):
-    _fields_ = [(n, C.c_void_p) for n in ("point_list", "ranges", "n_contrib", "final_T", "packed", "tiles_touched", "clamped")]
+    _fields_ = [(n, C.c_void_p) for n in ("point_list", "ranges", "n_contrib", "final_T", "packed", "tiles_touched", "clamped", "warp_mask")]
 
 
 def _view(lib, f):

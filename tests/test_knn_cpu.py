@@ -1,8 +1,9 @@
 """Oracle of simple-knn's distCUDA2 (oracle/gs_next_oracle.c: gno_knn_mean_d2) against an independent exact search.
 
-The reference function is CUDA only and ships no vectors, so the oracle is not pinned to the reference binary this round
-("parity unpinned", see the oracle's header); its definition -- mean of the three smallest squared distances to other
-points -- is checked against scipy's cKDTree in float64.  CPU only."""
+The reference function is CUDA only and ships no vectors; the oracle is PINNED to the reference binary by the fixture its
+own sm_100 build wrote on a B200 in round 2 (tests/golden/ref_knn_cuda.npz, tests/golden/make_golden_knn_gpu.py), bit for
+bit -- that fixture is what exposed the y-first contraction of the distance.  Its definition -- mean of the three smallest
+squared distances to other points -- is also checked against scipy's cKDTree in float64.  CPU only."""
 import numpy as np
 import pytest
 from scipy.spatial import cKDTree
@@ -46,14 +47,13 @@ def test_scale_initialisation_expression_of_the_reference():
     assert np.allclose(np.log(np.sqrt(d2)), np.log(np.sqrt(1e-7)))
 
 
-def test_oracle_reproduces_the_reference_build_when_its_fixture_exists():
+def test_oracle_reproduces_the_reference_builds_b200_fixture_bit_for_bit():
     """tests/golden/ref_knn_cuda.npz comes from the reference's own simple-knn on a B200 (tests/golden/make_golden_knn_gpu.py).
-    Not generated yet at the end of round 1 (no GPU minutes left): skipped until it is committed."""
+    Six cases: coincident points, anisotropic and two-scale clouds, 3 and 4 points, one point past a 1024-box edge."""
     import os
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_knn_cuda.npz")
-    if not os.path.exists(path):
-        pytest.skip("fixture from the reference's CUDA build not generated yet (needs a GPU run)")
     z = np.load(path)
+    assert sum(k.startswith("pts_") for k in z.files) == 6
     for k in z.files:
         if k.startswith("pts_"):
             assert np.array_equal(O.knn_mean_dist2(z[k]), z["d2_" + k[4:]]), k

@@ -97,10 +97,10 @@ def bench_adam(P, steps, warmup):
 
 
 def ref_knn_module():
-    so = os.path.join(ROOT, "oracle", "_ref", "simple_knn", "_C.so")
+    so = os.path.join(ROOT, "oracle", "_ref", "simple_knn", "ref_simple_knn_C.so")
     if not os.path.exists(so):
         return None
-    spec = importlib.util.spec_from_file_location("_C", so)
+    spec = importlib.util.spec_from_file_location("ref_simple_knn_C", so)
     m = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(m)
     return m
