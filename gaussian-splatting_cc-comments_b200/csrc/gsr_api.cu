@@ -65,6 +65,7 @@ struct Readback { cudaStream_t side = nullptr; cudaEvent_t produced = nullptr, c
 static thread_local Readback g_readback[GSR_MAX_DEVICES];
 
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+namespace gsr { int set_error(int code, const std::string& msg) { return fail(code, msg); } }   // for entry points in other files
 
 #define GSR_CUDA(call)                                                                         \
     do {                                                                                       \

@@ -4,6 +4,7 @@
 // to callers, as in the reference: DGR/cuda_rasterizer/rasterizer_impl.h:33-81).
 #pragma once
 #include <cuda_runtime.h>
+#include <string>
 #include <stdint.h>
 #include <stddef.h>
 
@@ -118,6 +119,7 @@ struct ImageState {
 };
 
 void count_launch(int n);   // bumps the library-wide kernel launch counter (gsr_launch_count)
+int set_error(int code, const std::string& msg);   // stores the text gsr_last_error() returns (thread-local), returns `code`
 
 // ---- stage launchers (each enqueues on `st`, none synchronises) --------------------------------
 struct Camera {             // device pointers, read once per block

@@ -195,3 +195,61 @@ void launch_l1_ssim_backward(const float* img, const float* gt, const float* dm_
 }
 
 }  // namespace gsr
+
+// ---- gsr_l1_ssim_forward_noalloc: the forward above with its per-block partial sums in a file-scope device array ----
+// For callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart
+// in the reference (include/gsr.h).
+//
+// The array lives in every GPU context that loads this library until the process exits (1 MiB per GPU).  In HOST code
+// its name is only a stand-in for the symbol, not a device address: the address of this device's copy is fetched once per
+// device, with that device current, by cudaGetSymbolAddress and that pointer is what the kernels get.  The forward kernel
+// overwrites partial[0 .. 2*nblocks) completely and the finalize kernel reads exactly that range, so nothing has to be
+// cleared between calls; the array keeps the last call's partial sums.  Every call on a device shares it: two calls that
+// overlap on the GPU (different streams, no ordering between them) race on it.
+#include "../../include/gsr.h"
+#include <mutex>
+#include <string>
+
+namespace gsr {
+constexpr size_t L1_SSIM_NOALLOC_MAX_BLOCKS = GSR_L1_SSIM_NOALLOC_MAX_BLOCKS;
+static __device__ __align__(256) float g_l1_ssim_static_partial[2 * L1_SSIM_NOALLOC_MAX_BLOCKS];
+
+static std::mutex g_static_partial_mutex;
+static float* g_static_partial_ptr[GSR_MAX_DEVICES];      // device address of the array, per device ordinal (nullptr = not fetched)
+}  // namespace gsr
+
+extern "C" size_t gsr_l1_ssim_noalloc_max_blocks(void) { return gsr::L1_SSIM_NOALLOC_MAX_BLOCKS; }
+
+extern "C" int gsr_l1_ssim_forward_noalloc(const float* img, const float* gt, int planes, int height, int width, float lambda_dssim,
+                                           float* dm_maps, float* out3, void* cuda_stream) {
+    using namespace gsr;
+    if (planes <= 0 || height <= 0 || width <= 0) return set_error(GSR_ERR_INVALID_ARGUMENT, "bad image sizes");
+    if (!img || !gt || !out3) return set_error(GSR_ERR_INVALID_ARGUMENT, "null pointer");
+    if (planes > 65535) return set_error(GSR_ERR_INVALID_ARGUMENT, "image too large");
+    const size_t nb = l1_ssim_blocks(planes, height, width);
+    if (nb > L1_SSIM_NOALLOC_MAX_BLOCKS)
+        return set_error(GSR_ERR_INVALID_ARGUMENT,
+                         "gsr_l1_ssim_forward_noalloc: planes * ceil(H/16) * ceil(W/16) = " + std::to_string(nb) + " tiles exceed the static scratch of " +
+                             std::to_string(L1_SSIM_NOALLOC_MAX_BLOCKS) + " tiles; use gsr_l1_ssim_forward with caller-provided scratch");
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return set_error(GSR_ERR_CUDA, std::string("cudaGetDevice: ") + cudaGetErrorString(e));
+    if (dev < 0 || dev >= GSR_MAX_DEVICES) return set_error(GSR_ERR_INVALID_ARGUMENT, "device ordinal out of range");
+    float* partial = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_static_partial_mutex);
+        if (g_static_partial_ptr[dev] == nullptr) {      // once per device, with that device current
+            void* p = nullptr;
+            e = cudaGetSymbolAddress(&p, g_l1_ssim_static_partial);
+            if (e != cudaSuccess || p == nullptr)
+                return set_error(GSR_ERR_CUDA, std::string("cudaGetSymbolAddress(g_l1_ssim_static_partial): ") + cudaGetErrorString(e));
+            g_static_partial_ptr[dev] = (float*)p;
+        }
+        partial = g_static_partial_ptr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_l1_ssim_forward(img, gt, planes, height, width, lambda_dssim, dm_maps, partial, out3, st);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return set_error(GSR_ERR_CUDA, std::string("stage l1+ssim forward (noalloc): ") + cudaGetErrorString(e));
+    return GSR_OK;
+}

@@ -212,6 +212,23 @@ int gsr_l1_ssim_forward(const float* img, const float* gt, int planes, int heigh
 int gsr_l1_ssim_backward(const float* img, const float* gt, const float* dm_maps, int planes, int height, int width,
                          float coef_l1, float coef_ssim, const float* grad_out, float* dL_dimg, void* cuda_stream);
 
+/* gsr_l1_ssim_forward without caller scratch and WITHOUT ANY ALLOCATION (no cudaMalloc / cudaFree, no allocating library
+ * call): for callers that cannot allocate -- code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc.  It has NO counterpart in the reference.
+ * Same kernels, same arithmetic and the same outputs as gsr_l1_ssim_forward; the per-tile partial sums live in a
+ * file-scope `static __device__` array of this library (csrc/gsr_loss.cu): 2 * GSR_L1_SSIM_NOALLOC_MAX_BLOCKS floats =
+ * 1 MiB, held by every GPU context that loads the library until the process exits.
+ * Limit: planes * ceil(H/16) * ceil(W/16) <= GSR_L1_SSIM_NOALLOC_MAX_BLOCKS (131072 tiles: 3 x 3840 x 2160 needs 97200);
+ * larger images are rejected with GSR_ERR_INVALID_ARGUMENT and a text that names both numbers.
+ * The array is SHARED by every call on a device and keeps the last call's partial sums (each call overwrites the range it
+ * then reads, so nothing needs clearing): calls that OVERLAP on the GPU -- different streams without an ordering between
+ * them -- race on it.  The first call on each device fetches the array's device address (cudaGetSymbolAddress, that
+ * device current); call it with the device current on which img / gt / out3 live. */
+#define GSR_L1_SSIM_NOALLOC_MAX_BLOCKS 131072
+size_t gsr_l1_ssim_noalloc_max_blocks(void);
+int gsr_l1_ssim_forward_noalloc(const float* img, const float* gt, int planes, int height, int width, float lambda_dssim,
+                                float* dm_maps, float* out3, void* cuda_stream);
+
 /* ---- Fused Adam step over all parameter groups ----
  * Replaces `self.optimizer.step()` (train.py:173-175) for the optimizer scene/gaussian_model.py:243-252 builds:
  * torch.optim.Adam(l, lr=0.0, eps=1e-15), six groups, no weight decay, no amsgrad.  One kernel launch updates every group

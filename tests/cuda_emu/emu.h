@@ -32,6 +32,10 @@
 #define __device__
 #undef __forceinline__
 #define __forceinline__ inline
+#undef __align__
+#define __align__(n) __attribute__((aligned(n)))
+// a file-scope device array is a host array here, and its "device address" is its address
+template <class T> inline cudaError_t cudaGetSymbolAddress(void** p, T& symbol) { *p = (void*)&symbol; return cudaSuccess; }
 
 namespace emu {
 
