@@ -166,6 +166,8 @@ inline int __popc(unsigned x) { return __builtin_popcount(x); }
 template <typename T> inline T __ldg(const T* p) { return *p; }
 inline int __float_as_int(float f) { int i; std::memcpy(&i, &f, 4); return i; }
 inline float __int_as_float(int i) { float f; std::memcpy(&f, &i, 4); return f; }
+inline float __fdividef(float a, float b) { return a / b; }
+template <class F> inline cudaError_t cudaFuncSetAttribute(F*, cudaFuncAttribute, int) { return cudaSuccess; }   // launch hints mean nothing here
 inline unsigned __float_as_uint(float f) { unsigned i; std::memcpy(&i, &f, 4); return i; }
 inline float __uint_as_float(unsigned i) { float f; std::memcpy(&f, &i, 4); return f; }
 inline float __fmaf_rn(float a, float b, float c) { return std::fmaf(a, b, c); }
