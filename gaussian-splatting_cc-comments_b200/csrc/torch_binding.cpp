@@ -98,14 +98,15 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
     int64_t M = 0;
     if (sh.numel() != 0) M = sh.size(1);
     auto fopt = means3D.options().dtype(torch::kFloat32);
-    // one flat gradient arena; per-Gaussian widths: mean3D 3, mean2D 3, opacity 1, scale 3, rot 4 (the small live blocks,
-    // contiguous so that one all-reduce covers them), sh 3M, then the blocks training never reads: colour 3, cov3D 6, conic 4
+    // one flat gradient arena; per-Gaussian widths: mean2D 3 (never exchanged between ranks: densification takes per-view
+    // norms), then mean3D 3, opacity 1, scale 3, rot 4 (the small live blocks, contiguous so that ONE all-reduce covers
+    // them in multi-view training), sh 3M, then the blocks training never reads: colour 3, cov3D 6, conic 4
     const int64_t widths[9] = {3, 3, 1, 3, 4, 3 * M, 3, 6, 4};
     int64_t offs[10]; offs[0] = 0;
     for (int i = 0; i < 9; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;   // keep 16-byte alignment
     torch::Tensor flat = torch::empty({offs[9]}, fopt);
     auto view = [&](int i, std::vector<int64_t> shape) { return flat.narrow(0, offs[i], widths[i] * P).view(shape); };
-    torch::Tensor dL_dmeans3D = view(0, {P, 3}), dL_dmeans2D = view(1, {P, 3}), dL_dopacity = view(2, {P, 1}),
+    torch::Tensor dL_dmeans2D = view(0, {P, 3}), dL_dmeans3D = view(1, {P, 3}), dL_dopacity = view(2, {P, 1}),
                   dL_dscales = view(3, {P, 3}), dL_drotations = view(4, {P, 4}), dL_dsh = view(5, {P, M, 3}),
                   dL_dcolors = view(6, {P, 3}), dL_dcov3D = view(7, {P, 6}), dL_dconic = view(8, {P, 2, 2});
     if (P != 0) {

@@ -97,9 +97,9 @@ class _RasterizeGaussians(torch.autograd.Function):
             grads = _C.rasterize_gaussians_backward(*args, *band)
         (grad_means2D, grad_colors_precomp, grad_opacities, grad_means3D, grad_cov3Ds_precomp,
          grad_sh, grad_scales, grad_rotations) = grads
-        if mv is not None:   # gradients come back summed over the ranks' views
-            mv.exchange(_C, means3D, rs.sh_degree, grad_sh,
-                        (grad_means3D, grad_means2D, grad_opacities, grad_scales, grad_rotations))
+        if mv is not None:   # the SH gradient of the step's last local view is the sum over all views of all ranks
+            grad_sh = mv.exchange(_C, means3D, rs.sh_degree, grad_sh,
+                                  (grad_means3D, grad_means2D, grad_opacities, grad_scales, grad_rotations))
         return (grad_means3D, grad_means2D, grad_sh, grad_colors_precomp, grad_opacities,
                 grad_scales, grad_rotations, grad_cov3Ds_precomp, None)
 

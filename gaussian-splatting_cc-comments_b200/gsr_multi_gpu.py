@@ -195,29 +195,38 @@ def cameras_for_rank(n_views: int, rank: int, world: int) -> List[int]:
     return [c for c in range(n_views) if c % world == rank]
 
 
-class MultiViewExchange:
-    """Gradient exchange for multi-view training, one camera per rank.
+def exchange_block_floats(P: int) -> int:
+    """Floats of one view's exchange block: campos (4) | dL/dRGB (P,3), padded so that consecutive blocks stay 16-byte aligned
+    for any P (the SH kernel reads them with 16-byte loads)."""
+    return (4 + 3 * int(P) + 3) & ~3
 
-    Per view the SH gradient is an outer product basis(dir_v) (x) dL/dRGB_v, so the 12*M bytes per Gaussian of
-    dL_dsh never cross the links.  Each rank's backward publishes 12 bytes per Gaussian (clamp-masked dL/dRGB)
-    plus its camera position in a peer-mapped (symmetric memory) block as soon as the blending backward is done
-    and records an event.  From there two things run side by side:
-      * side stream: device barrier, then the 7 peers' blocks are pulled over NVLink by the copy engines (no SMs)
-        into local staging, second barrier (blocks may be overwritten again);
-      * main stream: the per-Gaussian backward (HBM/SM bound), which overlaps with those copies.
-    Then ONE kernel (`gsr_multiview_sh_grad`) rebuilds every view's SH basis and writes the summed dL_dsh, while
-    the 14 other live floats per Gaussian (means3D, means2D, opacity, scale, rotation -- contiguous in the
-    gradient arena) are summed by one NCCL all-reduce that overlaps with that kernel (NVLink vs SM/HBM).
-    NVLink traffic per GPU at 8 ranks, P = 3 M: 252 MB of peer copies + a 168 MB all-reduce, instead of a 744 MB
-    all-reduce.
+
+class MultiViewExchange:
+    """Gradient exchange for multi-view training: `views_per_rank` cameras per rank and step (SURVEY.md 8(e), C5:
+    8 cameras per step = 8/4/2/1 views per GPU at 1/2/4/8 GPUs).
+
+    Per view the SH gradient is an outer product basis(dir_v) (x) dL/dRGB_v, so the 12*M bytes per Gaussian of dL_dsh never
+    cross the links.  Every local backward publishes 12 bytes per Gaussian (clamp-masked dL/dRGB) plus its camera position
+    into its slot of this rank's block and skips dL_dsh.  The LAST local backward of a step then
+      * side stream: all-gathers the blocks (NCCL; or maps the peers' blocks, mode "peer") as soon as its dL/dRGB is
+        published -- beside the per-Gaussian backward the main stream is still running -- and ONE kernel
+        (`gsr_multiview_sh_grad`) rebuilds every view's SH basis and writes the dL_dsh summed over ALL views of ALL ranks;
+      * `end_step()` sums the 11 other live floats per Gaussian (means3D, opacity, scale, rotation: the parameters' .grad
+        after autograd has accumulated the local views) with one NCCL all-reduce that overlaps with that kernel.
+    means2D.grad is NOT exchanged: the reference's densification statistic is a per-view norm (scene/gaussian_model.py:599-602),
+    which each rank accumulates for its own views exactly as the reference does; `reduce_densification_stats(model)` sums
+    the accumulators over the ranks (and max-reduces max_radii2D, train.py:157) right before densify_and_prune.
+    NVLink traffic per GPU and step at 8 ranks, P = 3 M: 252 MB all-gather + a 132 MB all-reduce, instead of a 744 MB all-reduce.
     """
 
-    def __init__(self, capacity, device, group=None, mode=None):
+    def __init__(self, capacity, device, group=None, mode=None, views_per_rank=1):
         import os
-        import torch.distributed._symmetric_memory as symm_mem
         self.group = group if group is not None else dist.group.WORLD
         self.world = dist.get_world_size(self.group)
         self.rank = dist.get_rank(self.group)
+        self.views_per_rank = int(views_per_rank)
+        if self.views_per_rank < 1 or self.world * self.views_per_rank > 16:      # GSR_MAX_VIEWS
+            raise ValueError("views_per_rank * world must be in 1..16")
         self.device = torch.device(device)
         if self.device.index is None:
             self.device = torch.device("cuda", torch.cuda.current_device())
@@ -225,7 +234,10 @@ class MultiViewExchange:
         # kernel on local data; "peer" = plain peer loads inside the SH kernel (symmetric memory).  Measured on 8 B200:
         # 5.18 vs 5.36 ms per step (profiles/r01_multigpu_c5.md) -- the all-gather goes through NVLS.
         self.mode = mode or os.environ.get("GSR_MULTIVIEW_MODE", "allgather")
-        self._symm = symm_mem
+        self._symm = None
+        if self.mode != "allgather" or os.environ.get("GSR_MULTIVIEW_SMALL", "nccl") == "multimem":
+            import torch.distributed._symmetric_memory as symm_mem
+            self._symm = symm_mem
         # high priority: the exchange's few CTAs must be dispatched WHILE the per-Gaussian backward (tens of thousands of
         # short blocks, launched earlier) is running, not after it.  For the NCCL part set TORCH_NCCL_HIGH_PRIORITY=1
         # before init_process_group (bench.py does).
@@ -247,6 +259,8 @@ class MultiViewExchange:
         # GSR_MV_TIMELINE=1: timed events around every phase of the exchange (diagnostics; see timeline_report)
         self._tl = [] if os.environ.get("GSR_MV_TIMELINE") == "1" else None
         self._tl_cur = None
+        self._view = 0                  # local views whose backward has run in the current step
+        self._pending_done = False      # the SH kernel of this step is still running on the side stream
         self._alloc(int(capacity))
 
     def _mark(self, name, stream=None):
@@ -262,6 +276,8 @@ class MultiViewExchange:
         torch.cuda.synchronize(self.device)
         acc = {}
         for marks in self._tl[skip:]:
+            if not marks:
+                continue
             t0 = marks[0][1]
             for name, e in marks[1:]:
                 acc.setdefault(name, []).append(t0.elapsed_time(e))
@@ -269,16 +285,16 @@ class MultiViewExchange:
 
     def _alloc(self, capacity):
         self.capacity = capacity
-        n = 4 + 3 * capacity
+        n = exchange_block_floats(capacity) * self.views_per_rank
         # (P,14) small-gradient rows.  "multimem": symmetric allocation bound to an NVLS multicast address, summed by
-        # this package's own two-shot kernel through the switch (gsr_multimem_allreduce); "nccl": plain tensor, NCCL
-        # all-reduce of each range.  multimem needs NVSwitch multicast support; it falls back by itself (collectively:
-        # every rank sees the same answer from the rendezvous).
-        self.pack_handle, self.pack_mc = None, 0
-        # Default "nccl": on 8 B200 the multimem kernel of this round needs 0.3-0.4 ms for its 21 MB slice and the step
-        # ends later (4.34 ms vs 4.01 ms, profiles/r01_multigpu_c5.md); it stays selectable for the next round's work.
+        # this package's own two-shot kernel through the switch (gsr_multimem_allreduce); "nccl": the parameters' .grad,
+        # NCCL all-reduce.  multimem needs NVSwitch multicast support and one view per rank; it falls back by itself
+        # (collectively: every rank sees the same answer from the rendezvous).
+        self.pack_handle, self.pack_mc, self.pack = None, 0, None
+        # Default "nccl": on 8 B200 the multimem kernel needs 0.3-0.4 ms for its 21 MB slice and the step ends later
+        # (4.34 ms vs 4.01 ms, profiles/r01_multigpu_c5.md); it stays selectable.
         want = os.environ.get("GSR_MULTIVIEW_SMALL", "nccl")
-        if want == "multimem":
+        if want == "multimem" and self.views_per_rank == 1:
             try:
                 self.pack = self._symm.empty(14 * capacity, dtype=torch.float32, device=self.device)
                 self.pack.zero_()
@@ -289,8 +305,7 @@ class MultiViewExchange:
                 if self.rank == 0:
                     print("gsr_multi_gpu: multimem exchange unavailable (%s); using NCCL for the small gradients" % (e,), file=sys.stderr)
         if not self.pack_mc:
-            self.pack_handle = None
-            self.pack = torch.zeros(14 * capacity, dtype=torch.float32, device=self.device)
+            self.pack_handle, self.pack = None, None
         self.small_mode = "multimem" if self.pack_mc else "nccl"
         if self.mode == "allgather":
             self.block = torch.zeros(n, dtype=torch.float32, device=self.device)
@@ -303,21 +318,36 @@ class MultiViewExchange:
             self.peer_ptrs = [int(p) for p in self.handle.buffer_ptrs]
             self.stage = None
 
+    # ---- called by _RasterizeGaussians.backward ------------------------------------------------------------------
     def backward_extra(self, P, campos):
-        """Called by the backward before its kernels: (exchange block with campos written, skip_dsh, event handle)."""
+        """Before the backward's kernels: (this view's exchange block with campos written, skip_dsh, event handle, chunk
+        events, small pack)."""
+        if self._view >= self.views_per_rank:
+            raise RuntimeError("MultiViewExchange: more than views_per_rank = %d backward passes in one step; call end_step() "
+                               "after the step's last backward" % self.views_per_rank)
         if P > self.capacity:                     # densification grew the model: same P on every rank, so this is collective
             self._alloc(int(P * 1.25) + 1024)
-        self.block[:3].copy_(campos.reshape(-1)[:3], non_blocking=True)
-        if self._tl is not None:
+        nb = exchange_block_floats(P)
+        blk = self.block[self._view * nb:(self._view + 1) * nb]
+        blk[:3].copy_(campos.reshape(-1)[:3], non_blocking=True)
+        last = self._view == self.views_per_rank - 1
+        if self._tl is not None and last:
             self._tl_cur = []
             self._tl.append(self._tl_cur)
             self._mark("backward_start")
-        return (self.block, True, int(self.ev_drgb.cuda_event), [int(e.cuda_event) for e in self.ev_chunk],
-                self.pack if self.small_mode == "multimem" else None)
+        # chunk events / packed rows only matter for the backward the exchange runs beside: the step's last one
+        return (blk, True, int(self.ev_drgb.cuda_event) if last else 0, [int(e.cuda_event) for e in self.ev_chunk] if last else [],
+                self.pack if (self.small_mode == "multimem" and last) else None)
 
     def exchange(self, C, means3D, sh_degree, grad_sh, small_grads):
+        """After a local backward's kernels are queued.  Returns the SH gradient autograd gets for this view: None for all but
+        the step's last local view (their share arrives with the last one), the sum over ALL views for the last."""
+        self._view += 1
+        if self._view < self.views_per_rank:
+            return None
         P = means3D.shape[0]
-        n = 4 + 3 * P
+        nb = exchange_block_floats(P)
+        n = nb * self.views_per_rank
         main = torch.cuda.current_stream(self.device)
         # side stream: starts as soon as dL/dRGB is published (event recorded by gsr_backward right after the blending
         # backward), i.e. it runs beside the per-Gaussian backward that the main stream is still executing
@@ -330,56 +360,78 @@ class MultiViewExchange:
                 dist.all_gather_into_tensor(out, self.block[:n], group=self.group)
                 self.ev_ag.record(self.side)
                 self._mark("allgather_done", self.side)
-                ptrs = [out[r * n:].data_ptr() for r in range(self.world)]
+                ptrs = [out[i * nb:].data_ptr() for i in range(self.world * self.views_per_rank)]
                 C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
                 self._mark("sh_kernel_done", self.side)
             else:
                 self.handle.barrier(channel=0)    # every rank's dL/dRGB and campos are in place
                 self.ev_ag.record(self.side)
                 # start with the next rank's block so that the ranks do not all pull from the same GPU at once
-                ptrs = [self.peer_ptrs[(self.rank + 1 + i) % self.world] for i in range(self.world)]
+                ptrs = [self.peer_ptrs[(self.rank + 1 + i) % self.world] + 4 * v * nb
+                        for i in range(self.world) for v in range(self.views_per_rank)]
                 C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
                 self.handle.barrier(channel=1)    # nobody overwrites a block a peer is still reading
             self.ev_done.record(self.side)
-        # The 14 other live floats per Gaussian.  The links carry one thing at a time: first the all-gather above (it
-        # gates the SH kernel, the longest tail), then this sum -- measured on 8 B200, running both at once doubles the
-        # all-gather's time and the step ends later (profiles/r01_multigpu_c5.md).
-        g3d, g2d, gop, gsc, grot = small_grads
+        self._pending_done = True
         if self.small_mode == "multimem":
-            # rows of the symmetric (P,14) block, summed through the switch by this package's own kernel
+            # one view per rank: rows of the symmetric (P,14) block, summed through the switch by this package's own kernel
             # (multimem.ld_reduce + multimem.st on this rank's 1/world slice), then scattered into the five tensors
+            g3d, g2d, gop, gsc, grot = small_grads
+            g2d_own = g2d.clone()                 # means2D is not an exchanged quantity: keep this view's
             self.comm.wait_event(self.ev_ag)
             self.comm.wait_event(self.ev_chunk[-1])          # the per-Gaussian backward has written every row
             with torch.cuda.stream(self.comm):
                 self._mark("small_start", self.comm)
                 self.pack_handle.barrier(channel=2)          # ... on every rank
-                self._mark("small_barrier_in", self.comm)
                 C.multimem_allreduce(self.pack_mc, 0, 14 * int(P), self.rank, self.world, self.device.index)
                 self._mark("small_reduced", self.comm)
                 self.pack_handle.barrier(channel=3)          # every rank's slice is reduced and broadcast
-                self._mark("small_barrier_out", self.comm)
                 C.unpack_small_grads(0, int(P), self.pack, g3d, g2d, gop, gsc, grot)
             self.ev_small.record(self.comm)
             main.wait_event(self.ev_small)
-        else:
-            # NCCL: one all-reduce of the contiguous small block of the gradient arena, on the main stream (ordered
-            # after the per-Gaussian backward; NCCL runs it behind the all-gather on its own stream)
-            span = flat_span(small_grads)
-            if span is not None:
+            g2d.copy_(g2d_own)
+        return grad_sh
+
+    # ---- called by the training loop -----------------------------------------------------------------------------
+    def end_step(self, small_params):
+        """After the step's last `backward()`: sums the .grad of `small_params` (means3D, opacities, scales, rotations --
+        whatever is passed, NOT means2D and not the SH tensor) over the ranks with one all-reduce when they share the
+        backward's flat arena (else one per tensor), then joins the SH kernel.  Collective."""
+        if self._view != self.views_per_rank:
+            raise RuntimeError("MultiViewExchange.end_step: %d of %d local views have run" % (self._view, self.views_per_rank))
+        main = torch.cuda.current_stream(self.device)
+        if self.small_mode != "multimem":
+            grads = [p.grad for p in small_params if p.grad is not None]
+            # The links carry one thing at a time: first the all-gather (it gates the SH kernel, the longest tail), then
+            # this sum -- NCCL runs it behind the all-gather on its own stream; it overlaps with the SH kernel.
+            span = flat_span(grads)
+            if span is not None and span.numel() <= sum(g.numel() for g in grads) + 16 * len(grads):
                 dist.all_reduce(span, op=dist.ReduceOp.SUM, group=self.group)
             else:
-                for g in small_grads:
+                for g in grads:
                     dist.all_reduce(g, op=dist.ReduceOp.SUM, group=self.group)
         self._mark("allreduce_done", main)
-        main.wait_event(self.ev_done)
+        if self._pending_done:
+            main.wait_event(self.ev_done)
+            self._pending_done = False
         self._mark("exchange_done", main)
+        self._view = 0
+
+    def reduce_densification_stats(self, model):
+        """Right before densify_and_prune: every rank has accumulated xyz_gradient_accum / denom (per-view norms and counts,
+        scene/gaussian_model.py:599-602) and max_radii2D (train.py:157) for ITS views; sums / max-reduces them so that all
+        ranks take the same decisions.  Collective; 12 bytes per Gaussian, once per densification interval."""
+        dist.all_reduce(model.xyz_gradient_accum, op=dist.ReduceOp.SUM, group=self.group)
+        dist.all_reduce(model.denom, op=dist.ReduceOp.SUM, group=self.group)
+        dist.all_reduce(model.max_radii2D, op=dist.ReduceOp.MAX, group=self.group)
 
 
-def enable_multiview_training(capacity, device, group=None, mode=None):
-    """Install the fused exchange: from now on `loss.backward()` through GaussianRasterizer returns gradients summed
-    over the ranks of `group` (each rank renders its own camera).  Collective.  Returns the exchange object."""
+def enable_multiview_training(capacity, device, group=None, mode=None, views_per_rank=1):
+    """Install the fused exchange: every rank runs `views_per_rank` forward/backward passes per step (its cameras) and then
+    calls `ex.end_step([means3D, opacities, scales, rotations])`; the SH gradient of the step's last backward and the .grad
+    of those parameters are then summed over all views of all ranks of `group`.  Collective.  Returns the exchange object."""
     import diff_gaussian_rasterization as dgr
-    ex = MultiViewExchange(capacity, device, group, mode)
+    ex = MultiViewExchange(capacity, device, group, mode, views_per_rank)
     dgr.set_multiview_exchange(ex)
     return ex
 

@@ -66,6 +66,15 @@ def test_banded_settings_keeps_the_reference_fields():
     assert b.tile_rows == (1, 2) and b.image_width == 48
 
 
+def test_exchange_blocks_stay_16_byte_aligned_for_any_P():
+    """One view's block is campos (4 floats) + dL/dRGB (3P floats), padded: consecutive blocks of an all-gather must start on
+    16-byte boundaries whatever P is (the SH kernel reads them with 16-byte loads; P changes at every densification)."""
+    for P in list(range(0, 70)) + [40000, 40001, 40002, 40003, 2999999, 3000000, 3000001]:
+        n = MG.exchange_block_floats(P)
+        assert n % 4 == 0 and 4 + 3 * P <= n < 4 + 3 * P + 4
+    assert MG.cameras_for_rank(8, 1, 4) == [1, 5] and MG.cameras_for_rank(8, 7, 8) == [7] and MG.cameras_for_rank(8, 0, 1) == list(range(8))
+
+
 def _free_port():
     s = socket.socket()
     s.bind(("127.0.0.1", 0))
@@ -97,7 +106,15 @@ def _worker(rank, world, port, q):
         p0, p1 = MG.band_pixel_rows(bands[rank], H)
         img = MG.gather_bands(full[:, p0:p1].contiguous(), bands, H)
         ok4 = bool((img == full).all())
-        q.put((rank, ok1, ok2, ok3, ok4))
+        # (4) densification statistics of multi-view training: per-rank accumulators of per-view norms / counts are summed,
+        #     max_radii2D max-reduced, so every rank takes the same clone / split / prune decisions
+        import types
+        m = types.SimpleNamespace(xyz_gradient_accum=torch.tensor([[1.0 + rank], [0.0], [2.0]]), denom=torch.tensor([[1.0], [0.0], [float(rank)]]),
+                                  max_radii2D=torch.tensor([3.0 * rank, 7.0 - rank, 0.0]))
+        MG.MultiViewExchange.reduce_densification_stats(types.SimpleNamespace(group=None), m)
+        ok5 = m.xyz_gradient_accum.flatten().tolist() == [3.0, 0.0, 4.0] and m.denom.flatten().tolist() == [2.0, 0.0, 1.0] \
+            and m.max_radii2D.tolist() == [3.0, 7.0, 0.0]
+        q.put((rank, ok1, ok2, ok3, ok4, ok5))
     finally:
         dist.destroy_process_group()
 

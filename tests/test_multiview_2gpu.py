@@ -1,5 +1,6 @@
-"""Multi-view training exchange on TWO real GPUs (NCCL + symmetric memory): gradients returned by backward() with the
-fused exchange enabled must equal the sum of the two ranks' single-view gradients.  Skipped with fewer than 2 GPUs."""
+"""Multi-view training exchange on TWO real GPUs (NCCL + symmetric memory): the gradients after the step's last backward()
+and end_step() with the fused exchange enabled must equal the sum of all views' single-view gradients, for one and two
+views per rank.  Skipped with fewer than 2 GPUs (bench.py runs the same check before its timed region at N > 1)."""
 import os
 import socket
 
@@ -28,25 +29,16 @@ def _worker(rank, world, port, q):
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
     try:
         import bench as B
-        import gsr_multi_gpu as MG
         mod = Hh.my_module()
-        P, W, H = 40000, 320, 200
-        scene = S.make_scene(P, S.make_camera(W, H), sh_degree=3, M=16, seed=4)
-        cams = [B.ring_camera(S, W, H, r) for r in range(world)]
-        dLs = [S.upstream_grad(c, seed=20 + i) for i, c in enumerate(cams)]
-        dev = "cuda:%d" % rank
-        # every rank computes every view locally (no exchange) -> the expected sum
-        expect = None
-        for c, dL in zip(cams, dLs):
-            g = Hh.run_torch(mod, c, scene, dL, bg=(0.1, 0.2, 0.3), device=dev)["grads"]
-            expect = g if expect is None else {k: (expect[k] + g[k] if g[k] is not None else None) for k in g}
+        dev = torch.device("cuda", rank)
         errs = {}
+        # bench.exchange_check: every rank computes every view locally (no exchange) -> the expected sum, then runs its own
+        # views through the fused exchange twice.  One and two views per rank, both transports, odd P (block alignment).
         for mode in ("allgather", "peer"):
-            MG.enable_multiview_training(P, dev, mode=mode)
-            got = Hh.run_torch(mod, cams[rank], scene, dLs[rank], bg=(0.1, 0.2, 0.3), device=dev)["grads"]
-            MG.disable_multiview_training()
-            errs.update({mode + "/" + k: float(Hh.rel_l2(got[k], expect[k]))
-                         for k in ("means3D", "means2D", "shs", "opacities", "scales", "rotations")})
+            os.environ["GSR_MULTIVIEW_MODE"] = mode
+            for vpr in (1, 2):
+                r = B.exchange_check(mod, dev, rank, world, vpr, P=40001)
+                errs["%s/vpr%d" % (mode, vpr)] = r["max_rel_l2"]
         q.put((rank, errs))
     finally:
         dist.destroy_process_group()

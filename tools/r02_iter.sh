@@ -3,7 +3,7 @@ set -u
 TAG=${1:-iter}
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_parity_gpu.py -m gpu -x -q 2>&1 | tail -4 | tee gpurun_out/r02_pytest_parity_$TAG.log
-timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline > gpurun_out/r02_bench_c2_$TAG.json 2> gpurun_out/r02_bench_c2_$TAG.err; echo "bench rc=$?"
+timeout 300 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-extras > gpurun_out/r02_bench_c2_$TAG.json 2> gpurun_out/r02_bench_c2_$TAG.err; echo "bench rc=$?"
 python - <<PY
 import json
 j = json.loads(open("gpurun_out/r02_bench_c2_$TAG.json").read().strip().splitlines()[-1])

@@ -4,7 +4,7 @@ mkdir -p gpurun_out
 for v in ${VARIANTS:-0 1 2 3 4 5 6 7}; do
   echo "== GSR_RB_VARIANT=$v"
   GSR_RB_VARIANT=$v timeout 300 python -m pytest tests/test_parity_gpu.py -m gpu -x -q -k "${PARITY_K:-reference_build}" 2>&1 | tail -1
-  GSR_RB_VARIANT=$v timeout 200 python bench.py --steps 20 --warmup 5 --no-cpu-baseline 2> gpurun_out/exp.err | python -c "
+  GSR_RB_VARIANT=$v timeout 200 python bench.py --steps 20 --warmup 5 --no-cpu-baseline --no-extras 2> gpurun_out/exp.err | python -c "
 import json,sys
 j=json.loads(sys.stdin.read().strip().splitlines()[-1]); print(round(j['ms_per_step'],4), j.get('fwd_ms'), j.get('bwd_ms'), {k:round(v['ms'],4) for k,v in j['stages'].items() if k in ('render','render_bwd','preprocess_bwd')})"
 done 2>&1 | tee gpurun_out/r02_sweep_rb.log

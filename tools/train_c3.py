@@ -55,7 +55,7 @@ def cameras(W, H, n):
     return cams
 
 
-def main():
+def parse_args(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--P0", type=int, default=1_000_000)
@@ -66,7 +66,11 @@ def main():
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--views", type=int, default=8)
-    a = ap.parse_args()
+    return ap.parse_args(argv)
+
+
+def run(a):
+    """One arm of the C3 loop; returns the record main() prints (bench.py embeds a compact form of it)."""
     assert torch.cuda.is_available(), "train_c3.py needs a GPU (there is no CPU path)"
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
@@ -108,13 +112,17 @@ def main():
     wall = time.time() - t0
     buckets = T.geometric_buckets(table)
     plain = [sum(r) for p, r in table]
-    print(json.dumps({
+    return ({
         "metric": "training ms/iter vs P, synthetic scene densifying %d -> %d Gaussians, SH3, %dx%d, 1 view/iter" % (a.P0, a.target, a.width, a.height),
         "impl": a.impl, "unit": "ms/iter", "higher_is_better": False, "data": "synthetic", "dtype": "f32",
         "config": {"workload": "c3-train-loop", "P0": a.P0, "P_target": a.target, "iterations": a.iterations, "views": a.views,
                    "densify_from": a.densify_from, "densify_every": a.densify_every,
                    "threshold": "quantile schedule (see tools/c3_trainer.py), not the reference's fixed 0.0002"},
-        "value": float(np.mean(plain)), "final_P": g.P, "wall_s": wall, "buckets": buckets, "densifications": log}))
+        "value": float(np.mean(plain)), "final_P": g.P, "wall_s": wall, "buckets": buckets, "densifications": log})
+
+
+def main():
+    print(json.dumps(run(parse_args())))
 
 
 if __name__ == "__main__":
