@@ -122,7 +122,13 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
             const float px = ndc2pix(projx, a.W), py = ndc2pix(projy, a.H);
             uint32_t x0, y0, x1, y1;
             get_rect(px, py, irad, (uint32_t)a.grid_x, (uint32_t)a.grid_y, x0, y0, x1, y1);
-            if ((x1 - x0) * (y1 - y0) != 0) {
+            // band-clipped tile count (tile-row sharded rendering); the full grid by default, then band_tiles is the whole rect
+            const uint32_t by0 = max(y0, (uint32_t)a.row_begin), by1 = min(y1, (uint32_t)a.row_end);
+            const uint32_t band_tiles = (by1 > by0) ? (by1 - by0) * (x1 - x0) : 0u;
+            // radii are those of the full image on every rank; a Gaussian that misses this rank's band emits nothing, so its
+            // SH row is not even read and no record is written (render-only sharding: 7/8 of the SH traffic at 8 ranks)
+            if ((x1 - x0) * (y1 - y0) != 0) out_radius = irad;
+            if (band_tiles != 0) {
                 // ---- colour -------------------------------------------------------------------
                 float rgb[3];
                 uint32_t clampbits = 0;
@@ -186,11 +192,15 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
                 rec[2] = make_float4(rgb[1], rgb[2], ext_x, ext_y);
                 a.clamped[idx] = (uint8_t)clampbits;
 
-                out_radius = irad;
-                // band-clipped tile count (tile-row sharded rendering); full grid by default
-                const uint32_t by0 = max(y0, (uint32_t)a.row_begin), by1 = min(y1, (uint32_t)a.row_end);
-                out_tiles = (by1 > by0) ? (by1 - by0) * (x1 - x0) : 0u;
-                if (out_tiles) out_key = __float_as_uint(depth);
+                out_tiles = band_tiles;
+                out_key = __float_as_uint(depth);
+            } else if (out_radius != 0) {
+                // visible, but not in this rank's band: a neutral record (a banded backward reads it beside all-zero accumulators)
+                float4* rec = a.packed + 3 * (size_t)idx;
+                rec[0] = make_float4(px, py, 0.f, 0.f);
+                rec[1] = make_float4(0.f, 1.0f, 0.f, 0.f);
+                rec[2] = make_float4(0.f, 0.f, -1.0f, -1.0f);
+                a.clamped[idx] = 0;
             }
         }
     }
