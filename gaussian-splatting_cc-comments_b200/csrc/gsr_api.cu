@@ -12,6 +12,7 @@
 #include <string>
 #include <cstdio>
 #include <atomic>
+#include <mutex>
 
 using namespace gsr;
 
@@ -23,38 +24,55 @@ enum Stage { ST_PREPROCESS = 0, ST_DEPTH_SORT, ST_SCAN, ST_DUPLICATE, ST_TILE_SO
              ST_BWD_ZERO, ST_RENDER_BWD, ST_PREPROCESS_BWD, ST_COUNT };
 static const char* const k_stage_names[ST_COUNT] = {"preprocess", "depth_sort", "scan", "duplicate", "tile_sort", "tile_ranges",
                                                     "render", "bwd_zero", "render_bwd", "preprocess_bwd"};
-static int g_profiling = 0;
-static cudaEvent_t g_ev[ST_COUNT][2];
-static bool g_ev_made = false, g_ev_pending[ST_COUNT];
-static double g_stage_sum_ms[ST_COUNT];
-static int g_stage_n[ST_COUNT], g_stage_dropped[ST_COUNT];
+// Per-device profiling state (one process may drive several devices, from several threads): events belong to the device
+// they were created on, and the means are kept per device.  gsr_get_stage_ms reports the calling thread's current device.
+static std::atomic<int> g_profiling{0};
+struct StageProf {
+    std::mutex mu;
+    cudaEvent_t ev[ST_COUNT][2];
+    bool made = false, pending[ST_COUNT] = {};
+    double sum_ms[ST_COUNT] = {};
+    int n[ST_COUNT] = {}, dropped[ST_COUNT] = {};
+};
+static StageProf g_prof[GSR_MAX_DEVICES];
+static StageProf* current_prof() {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= GSR_MAX_DEVICES) return nullptr;
+    return &g_prof[dev];
+}
 
-// Fold a finished (start, stop) pair of stage s into its running mean.  Never blocks unless `wait`.
-static void harvest_stage(int s, bool wait) {
-    if (!g_ev_made || !g_ev_pending[s]) return;
-    cudaError_t q = wait ? cudaEventSynchronize(g_ev[s][1]) : cudaEventQuery(g_ev[s][1]);
+// Fold a finished (start, stop) pair of stage s into its running mean.  Never blocks unless `wait`.  Caller holds p.mu.
+static void harvest_stage(StageProf& p, int s, bool wait) {
+    if (!p.made || !p.pending[s]) return;
+    cudaError_t q = wait ? cudaEventSynchronize(p.ev[s][1]) : cudaEventQuery(p.ev[s][1]);
     if (q == cudaSuccess) {
         float ms = 0.f;
-        if (cudaEventElapsedTime(&ms, g_ev[s][0], g_ev[s][1]) == cudaSuccess) { g_stage_sum_ms[s] += ms; g_stage_n[s]++; }
+        if (cudaEventElapsedTime(&ms, p.ev[s][0], p.ev[s][1]) == cudaSuccess) { p.sum_ms[s] += ms; p.n[s]++; }
     } else {
         if (q == cudaErrorNotReady) (void)cudaGetLastError();
-        g_stage_dropped[s]++;
+        p.dropped[s]++;
     }
-    g_ev_pending[s] = false;
+    p.pending[s] = false;
 }
 
 struct StageTimer {        // records start/stop events around one stage on the launching stream
-    int s; cudaStream_t st; bool on;
-    StageTimer(int stage, cudaStream_t stream) : s(stage), st(stream), on(g_profiling != 0) {
-        if (!on) return;
-        if (!g_ev_made) {
-            for (int i = 0; i < ST_COUNT; i++) { cudaEventCreate(&g_ev[i][0]); cudaEventCreate(&g_ev[i][1]); g_ev_pending[i] = false; }
-            g_ev_made = true;
+    int s; cudaStream_t st; StageProf* p;
+    StageTimer(int stage, cudaStream_t stream) : s(stage), st(stream), p(g_profiling.load(std::memory_order_relaxed) ? current_prof() : nullptr) {
+        if (!p) return;
+        std::lock_guard<std::mutex> lock(p->mu);
+        if (!p->made) {
+            for (int i = 0; i < ST_COUNT; i++) { cudaEventCreate(&p->ev[i][0]); cudaEventCreate(&p->ev[i][1]); p->pending[i] = false; }
+            p->made = true;
         }
-        harvest_stage(s, false);     // the previous step's pair for this stage has long finished (the forward syncs once)
-        cudaEventRecord(g_ev[s][0], st);
+        harvest_stage(*p, s, false);     // the previous step's pair for this stage has long finished (the forward syncs once)
+        cudaEventRecord(p->ev[s][0], st);
     }
-    ~StageTimer() { if (on) { cudaEventRecord(g_ev[s][1], st); g_ev_pending[s] = true; } }
+    ~StageTimer() {
+        if (!p) return;
+        std::lock_guard<std::mutex> lock(p->mu);
+        cudaEventRecord(p->ev[s][1], st);
+        p->pending[s] = true;
+    }
 };
 
 static thread_local std::string g_err;
@@ -96,17 +114,28 @@ int gsr_version(void) { return GSR_VERSION; }
 
 unsigned long long gsr_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 void gsr_set_profiling(int on) {
-    g_profiling = on;
-    if (on) for (int i = 0; i < ST_COUNT; i++) { g_stage_sum_ms[i] = 0.0; g_stage_n[i] = 0; g_stage_dropped[i] = 0; }
+    g_profiling.store(on, std::memory_order_relaxed);
+    if (on)
+        for (int d = 0; d < GSR_MAX_DEVICES; d++) {
+            std::lock_guard<std::mutex> lock(g_prof[d].mu);
+            for (int i = 0; i < ST_COUNT; i++) { g_prof[d].sum_ms[i] = 0.0; g_prof[d].n[i] = 0; g_prof[d].dropped[i] = 0; }
+        }
 }
 int gsr_num_stages(void) { return ST_COUNT; }
 const char* gsr_stage_name(int i) { return (i >= 0 && i < ST_COUNT) ? k_stage_names[i] : ""; }
 int gsr_get_stage_ms(float* mean_ms, int* samples, int n) {
     if (!mean_ms || n < ST_COUNT) return fail(GSR_ERR_INVALID_ARGUMENT, "need room for gsr_num_stages() entries");
+    StageProf* p = current_prof();
     for (int i = 0; i < ST_COUNT; i++) {
-        harvest_stage(i, true);
-        mean_ms[i] = g_stage_n[i] ? (float)(g_stage_sum_ms[i] / g_stage_n[i]) : -1.0f;
-        if (samples) samples[i] = g_stage_n[i];
+        if (p) {
+            std::lock_guard<std::mutex> lock(p->mu);
+            harvest_stage(*p, i, true);
+            mean_ms[i] = p->n[i] ? (float)(p->sum_ms[i] / p->n[i]) : -1.0f;
+            if (samples) samples[i] = p->n[i];
+        } else {
+            mean_ms[i] = -1.0f;
+            if (samples) samples[i] = 0;
+        }
     }
     return GSR_OK;
 }
