@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(32 * WPC, MINB) render_bwd_kernel(const uint2*
             const float un = mulr(dx, -a.w);
             const float2 s2 = fma2(bc2(dx), bc2(t1), mul2(dy, mul2(dy, bc2(b.x))));
             const float2 power = fma2(s2, bc2(-0.5f), mul2(dy, bc2(un)));
-            const float2 G0 = make_float2(expf(power.x), expf(power.y));
+            const float2 G0 = expf2(power);
             float2 al0 = mul2(bc2(b.z), G0);
             al0.x = fminf(0.99f, al0.x);
             al0.y = fminf(0.99f, al0.y);
