@@ -88,7 +88,7 @@ struct BinState {
     uint32_t* keys[2];         // R each: tile ids, ping-pong
     uint32_t* table;           // rs_blocks(R) * RS_BINS + 512
     uint32_t* scan_tmp;
-    uint8_t* warp_mask;        // R: bit w = warp w of the instance's tile blended it in the forward (backward's cull)
+    uint8_t* warp_mask;        // R: bit w (0..3) = 8x8 block w of the instance's tile blended it in the forward (backward's cull)
     size_t bytes;
     static BinState carve(char* base, size_t R) {
         BinState b; Carver c(base);

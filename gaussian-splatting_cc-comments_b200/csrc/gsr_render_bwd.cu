@@ -11,8 +11,8 @@
 //   * warps share nothing: no block barrier anywhere (a barrier per staging round cost 26 % of the warp
 //     time when four warps of a tile shared their staging, ncu r02_ncu_rbwd_v13a).  Each warp walks its
 //     tile's list back to front from its OWN last contributor in chunks of 32 positions; which (Gaussian,
-//     block) pairs carry a gradient comes from the warp masks the forward recorded (an 8x8 block = two of
-//     the forward's 8x4 blocks), so there is no geometric test and no empty replay, and only records that
+//     block) pairs carry a gradient comes from the warp masks the forward recorded (one bit per 8x8 block
+//     of the tile), so there is no geometric test and no empty replay, and only records that
 //     are replayed are fetched at all.
 //   * the walk is software-pipelined three deep: masks of chunk c+3 and ids of the hit positions of chunk
 //     c+2 are in flight in registers, the records of chunk c+1 travel by cp.async (LDGSTS) into the other of
@@ -159,8 +159,8 @@ __global__ void __launch_bounds__(32 * WPC, MINB) render_bwd_kernel(const uint2*
     const float2 npixfy = make_float2(-(float)pix_y0, -(float)pix_y1);         // a.y + (-py) == a.y - py
     const size_t id0 = (size_t)pix_y0 * W + pix_x, id1 = (size_t)pix_y1 * W + pix_x;
     const size_t HW = (size_t)H * W;
-    // the forward's 8x4 blocks: warp w' covers columns 8 (w' & 1), rows 4 (w' >> 1); this block is w' = bxi + 4 byi and that + 2
-    const uint32_t mbits = 0x5u << (bxi + 4 * byi);
+    // the forward records one bit per 8x8 block of the tile (its warp w' covers columns 8 (w' & 1), rows 8 (w' >> 1))
+    const uint32_t mbits = 1u << sub;
 
     const uint32_t list0 = ranges[tile_y * grid_x + tile_x].x;
 

@@ -329,7 +329,7 @@ typedef struct gsr_buffer_view {
     const float* packed;          /* (P,12) x,y,conic.xyz,power_thr,opacity,r,g,b,ext_x,ext_y   */
     const uint32_t* tiles_touched;/* (P)                                                        */
     const uint8_t* clamped;       /* (P) bit c set = colour channel c was clamped at 0          */
-    const uint8_t* warp_mask;     /* (R) bit w set = 8x4 pixel block w of the tile blended the instance (written by the forward) */
+    const uint8_t* warp_mask;     /* (R) bit w (0..3) set = 8x8 pixel block w of the tile blended the instance (written by the forward) */
 } gsr_buffer_view;
 
 int gsr_view_buffers(int P, int R, int width, int height, const char* geom_buffer,

@@ -35,17 +35,12 @@ def main():
     views = dgr._C.view_buffers(P, R, W, H, geom, binning, img)
     wm = views[7].to(torch.int32)
     nc = views[2].to(torch.int64)
-    pop = lambda x: sum(((x >> b) & 1) for b in range(8))
-    pairs84 = int(pop(wm).sum())
-    # 8x8 blocks: forward warp w covers x half (w & 1), row group (w >> 1) of 4 pixels; block b = (w & 1) + 2 * (w >> 2)
-    b88 = ((wm & 0b00000101) != 0).int() + ((wm & 0b00001010) != 0).int() + ((wm & 0b01010000) != 0).int() + ((wm & 0b10100000) != 0).int()
-    pairs88 = int(b88.sum())
-    # 16x4 strips (two 8x4 blocks side by side)
-    b164 = sum((((wm >> (2 * k)) & 3) != 0).int() for k in range(4))
+    # since v13 of the forward: one bit per 8x8 block of the tile (round 2 started with 8x4 blocks: 9 762 921 pairs at C2,
+    # profiles/r02_mask_stats.json)
+    pop = lambda x: sum(((x >> b) & 1) for b in range(4))
+    pairs88 = int(pop(wm).sum())
     out = {"P": P, "R": R, "visible": int((radii > 0).sum()), "instances_with_any_block": int((wm != 0).sum()),
-           "pairs_8x4": pairs84, "pairs_8x8": pairs88, "pairs_16x4": int(b164.sum()), "alpha_8x8": pairs88 / max(pairs84, 1),
-           "alpha_16x4": int(b164.sum()) / max(pairs84, 1), "sum_n_contrib": int(nc.sum()),
-           "blended_pixel_pairs_upper": int(nc.sum()), "pixel_slots_8x4": pairs84 * 32}
+           "pairs_8x8": pairs88, "sum_n_contrib": int(nc.sum()), "pixel_slots_8x8": pairs88 * 64}
     print(json.dumps(out))
 
 
