@@ -19,7 +19,7 @@
 //     two per-warp rings, while chunk c is replayed.
 //   * Phase 1 (lanes = pixels, sequential over the Gaussians of the block): only what needs the per-pixel
 //     recurrences (T, accumulated colour) is computed -- per pixel the two weights
-//         w   = opacity * G * dL/dalpha        (all positional / conic / opacity gradients are moments of w)
+//         w   = G * dL/dalpha                  (all positional / conic / opacity gradients are moments of w)
 //         dch = alpha * T                      (dL/dcolour = sum dch * dL/dpixel)
 //     and parked in shared memory, one 16-byte store per lane and replay, in a slot of an NS-slot batch.
 //   * Phase 2 (lanes = Gaussians, once per NS replays): lane (slot g, part h) walks its share of the
@@ -50,63 +50,59 @@ struct BwLayout {
     static constexpr int WP_BYTES = WP_DP + 32 * DP_ROW;
 };
 
-template <int OFF_E, int OFF_D>
-__device__ __forceinline__ void phase2_row(const uint32_t base, const uint32_t dbase, const float2 DX, const float2 DY, float2& S, float2& V0,
-                                           float2& V1, float2& V2, float2& V3, float2& V4, float2& V6, float2& V7, float2& V8) {
+// Phase 2, one pixel column of the lane's two rows: raw moments about the block centre.  X = column - 3.5 (exact).
+template <int OFF_E, int OFF_D, int COL>
+__device__ __forceinline__ void phase2_col(const uint32_t base, const uint32_t dbase, float2& S, float2& Mx, float2& Mxx, float2& V6, float2& V7,
+                                           float2& V8) {
     const float4 e = lds128<OFF_E>(base);
     const float2 d0 = lds64<OFF_D>(dbase), d1 = lds64<OFF_D + 8>(dbase), d2 = lds64<OFF_D + 16>(dbase);
     const float2 Wp = make_float2(e.x, e.y), Dc = make_float2(e.z, e.w);
-    const float2 WX = mul2(Wp, DX), WY = mul2(Wp, DY);
+    constexpr float X = (float)COL - 3.5f;
     S = add2(S, Wp);
-    V0 = add2(V0, WX);
-    V1 = add2(V1, WY);
-    V2 = fma2(WX, DX, V2);
-    V3 = fma2(WX, DY, V3);
-    V4 = fma2(WY, DY, V4);
+    Mx = fma2(Wp, bc2(X), Mx);
+    Mxx = fma2(Wp, bc2(X * X), Mxx);
     V6 = fma2(Dc, d0, V6);
     V7 = fma2(Dc, d1, V7);
     V8 = fma2(Dc, d2, V8);
 }
 
-template <int NS, int I, int SL_ROW, int DP_ROW>
-struct Phase2Rows {
-    static __device__ __forceinline__ void run(const uint32_t base, const uint32_t dbase, const float* dxs, const float2 dyA, const float2 dyB,
-                                               float2& S, float2& V0, float2& V1, float2& V2, float2& V3, float2& V4, float2& V6, float2& V7,
-                                               float2& V8) {
-        phase2_row<I * SL_ROW, I * DP_ROW>(base, dbase, bc2(dxs[I & 7]), I < 8 ? dyA : dyB, S, V0, V1, V2, V3, V4, V6, V7, V8);
-        Phase2Rows<NS, I + 1, SL_ROW, DP_ROW>::run(base, dbase, dxs, dyA, dyB, S, V0, V1, V2, V3, V4, V6, V7, V8);
-    }
-};
-template <int NS, int SL_ROW, int DP_ROW>
-struct Phase2Rows<NS, NS, SL_ROW, DP_ROW> {
-    static __device__ __forceinline__ void run(const uint32_t, const uint32_t, const float*, const float2, const float2, float2&, float2&, float2&,
-                                               float2&, float2&, float2&, float2&, float2&, float2&) {}
-};
-
-// Phase 2: the nine sums of the n <= NS Gaussians parked in this warp's slots.  Warp-uniform call.
-// Lane (slot g = lane % NS, part h = lane / NS) walks pixel lanes p = NS h + i, i = 0..NS-1 (two pixels each):
-//   NS = 16: column i & 7, rows 2h + (i >> 3) and that + 4;   NS = 8: column i, rows h and h + 4.
+// Phase 2: the nine sums of the n <= NS Gaussians parked in this warp's slots.  Warp-uniform call.  NS = 8:
+// lane (slot g = lane % 8, part h = lane / 8) walks the 8 pixel lanes of rows h and h + 4 of the block.  Per pixel only the
+// raw moments sum w, sum w x, sum w x^2 about the block centre are accumulated (x = column - 3.5 is a compile-time constant
+// and y is constant along a row); the moments about the Gaussian's centre the gradients need,
+//     sum w dx = ax S - Mx,   sum w dx^2 = ax^2 S - 2 ax Mx + Mxx,   sum w dy = dy S,   sum w dx dy = dy (ax S - Mx),   sum w dy^2 = dy^2 S
+// with ax = x_gaussian - x_centre, follow once per lane (a Gaussian that reaches the block has |ax| <= 3.5 + 3.4 sigma_x, so the
+// shift cancels at most one digit).  6 packed FP32 operations per pixel pair instead of 11: the kernel is co-bound by the FP32 pipes.
 template <int NS>
 __device__ __forceinline__ void flush_slots(const uint32_t wbuf, const int n, const int lane, const float fx0, const float fy0,
                                             float* __restrict__ grad_acc) {
+    static_assert(NS == 8, "phase 2 is written for 8 slots: 8 x 4 lanes = (slot, row pair)");
     using L = BwLayout<NS>;
     __syncwarp();
-    const int g = lane & (NS - 1), h = lane / NS;
+    const int g = lane & 7, h = lane >> 3;
     const float4 info = lds128<L::WP_SLOTS + L::SL_INFO>(wbuf + (uint32_t)g * L::SL_ROW);          // x, y, opacity, id
-    const float fyh = fy0 + (float)(NS == 16 ? 2 * h : h);
-    const float2 dyA = make_float2(subr(info.y, fyh), subr(info.y, fyh + 4.0f));
-    const float2 dyB = make_float2(subr(info.y, fyh + 1.0f), subr(info.y, fyh + 5.0f));     // NS = 16 only
-    float dxs[8];
-#pragma unroll
-    for (int i = 0; i < 8; i++) dxs[i] = subr(info.x, fx0 + (float)i);
-    const uint32_t base = wbuf + (uint32_t)(L::WP_SLOTS + h * NS * L::SL_ROW + g * 16);
-    const uint32_t dbase = wbuf + (uint32_t)(L::WP_DP + h * NS * L::DP_ROW);
-    float2 S = make_float2(0.f, 0.f), V0 = S, V1 = S, V2 = S, V3 = S, V4 = S, V6 = S, V7 = S, V8 = S;
-    Phase2Rows<NS, 0, L::SL_ROW, L::DP_ROW>::run(base, dbase, dxs, dyA, dyB, S, V0, V1, V2, V3, V4, V6, V7, V8);
-    float v0 = V0.x + V0.y, v1 = V1.x + V1.y, v2 = V2.x + V2.y, v3 = V3.x + V3.y, v4 = V4.x + V4.y, s = S.x + S.y;
+    const uint32_t base = wbuf + (uint32_t)(L::WP_SLOTS + h * 8 * L::SL_ROW + g * 16);
+    const uint32_t dbase = wbuf + (uint32_t)(L::WP_DP + h * 8 * L::DP_ROW);
+    float2 S = make_float2(0.f, 0.f), Mx = S, Mxx = S, V6 = S, V7 = S, V8 = S;
+    phase2_col<0 * L::SL_ROW, 0 * L::DP_ROW, 0>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<1 * L::SL_ROW, 1 * L::DP_ROW, 1>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<2 * L::SL_ROW, 2 * L::DP_ROW, 2>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<3 * L::SL_ROW, 3 * L::DP_ROW, 3>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<4 * L::SL_ROW, 4 * L::DP_ROW, 4>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<5 * L::SL_ROW, 5 * L::DP_ROW, 5>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<6 * L::SL_ROW, 6 * L::DP_ROW, 6>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<7 * L::SL_ROW, 7 * L::DP_ROW, 7>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    // shift to the Gaussian's centre (dx = x_g - x_pixel = ax - X, dy = y_g - y_row)
+    const float ax = subr(info.x, fx0 + 3.5f);
+    const float fyh = fy0 + (float)h;
+    const float2 dy = make_float2(subr(info.y, fyh), subr(info.y, fyh + 4.0f));
+    const float2 sdx = sub2(mul2(bc2(ax), S), Mx);                                   // sum w dx per row
+    const float2 sdxx = fma2(bc2(ax), sdx, fma2(bc2(-ax), Mx, Mxx));                 // sum w dx^2 per row
+    const float2 sdy = mul2(dy, S), sdxy = mul2(dy, sdx), sdyy = mul2(dy, sdy);
+    float v0 = sdx.x + sdx.y, v1 = sdy.x + sdy.y, v2 = sdxx.x + sdxx.y, v3 = sdxy.x + sdxy.y, v4 = sdyy.x + sdyy.y, s = S.x + S.y;
     float v6 = V6.x + V6.y, v7 = V7.x + V7.y, v8 = V8.x + V8.y;
 #pragma unroll
-    for (int d = 16; d >= NS; d >>= 1) {
+    for (int d = 16; d >= 8; d >>= 1) {
         v0 += __shfl_xor_sync(0xffffffffu, v0, d);
         v1 += __shfl_xor_sync(0xffffffffu, v1, d);
         v2 += __shfl_xor_sync(0xffffffffu, v2, d);
@@ -118,11 +114,12 @@ __device__ __forceinline__ void flush_slots(const uint32_t wbuf, const int n, co
         v8 += __shfl_xor_sync(0xffffffffu, v8, d);
     }
     if (lane < n) {        // part 0 lanes of the filled slots
-        // sum G dL/dalpha = (sum w) / opacity; opacity 0 never contributes (alpha = 0 < 1/255), then s = 0 as well
-        const float v5 = info.z != 0.0f ? __fdividef(s, info.z) : 0.0f;
+        // phase 1 parks w = G dL/dalpha; the moments carry the opacity factor (backward.cu:568: dL/dG = opacity dL/dalpha),
+        // the opacity gradient is the plain sum
+        const float op = info.z;
         float* dst = grad_acc + 12 * (size_t)__float_as_uint(info.w);
-        red_add_v4(dst, v0, v1, v2, v3);
-        red_add_v4(dst + 4, v4, v5, v6, v7);
+        red_add_v4(dst, op * v0, op * v1, op * v2, op * v3);
+        red_add_v4(dst + 4, op * v4, s, v6, v7);
         red_add_f32(dst + 8, v8);
     }
     __syncwarp();          // the slots are free again
@@ -171,11 +168,12 @@ __global__ void __launch_bounds__(32 * WPC, MINB) render_bwd_kernel(const uint2*
     if (in0) { dp0.x = dL_dpixels[id0]; dp1.x = dL_dpixels[HW + id0]; dp2.x = dL_dpixels[2 * HW + id0]; }
     if (in1) { dp0.y = dL_dpixels[id1]; dp1.y = dL_dpixels[HW + id1]; dp2.y = dL_dpixels[2 * HW + id1]; }
     const float bg0 = __ldg(bg), bg1 = __ldg(bg + 1), bg2 = __ldg(bg + 2);
-    // -T_final * (bg . dL/dpixel): the background term of dL/dalpha is this times 1 / (1 - alpha)
-    const float2 nTfbg = make_float2(-Tf0 * (bg0 * dp0.x + bg1 * dp1.x + bg2 * dp2.x), -Tf1 * (bg0 * dp0.y + bg1 * dp1.y + bg2 * dp2.y));
-    float2 ar0 = make_float2(0.f, 0.f), ar1 = ar0, ar2 = ar0;      // accum_rec per channel
-    float lc0 = 0.f, lc1 = 0.f, lc2 = 0.f;                          // last_color (the Gaussian's: same for both pixels)
-    float2 last_alpha = make_float2(0.f, 0.f);
+    // The background is the colour "behind everything": the reference's separate term -T_final / (1 - alpha) * (bg . dL/dpixel)
+    // of dL/dalpha (backward.cu:560-563) obeys the same recurrence as accum_rec, so it is folded into A's START value
+    // (B_j = -T_final (bg . dL/dpix) / T_after(j) satisfies B_j = (1 - alpha_{j+1}) B_{j+1}; A - B starts at bg . dL/dpix).
+    float2 A = make_float2(bg0 * dp0.x + bg1 * dp1.x + bg2 * dp2.x, bg0 * dp0.y + bg1 * dp1.y + bg2 * dp2.y);   // (accum_rec . dL/dpixel), background included
+    float2 Dl = make_float2(0.f, 0.f);                              // last_color . dL/dpixel
+    float2 last_alpha = make_float2(0.f, 0.f), last_oma = make_float2(1.f, 1.f);
 
     const uint32_t myrow = wbuf + WP_SLOTS + (uint32_t)lane * SL_ROW;
     {
@@ -267,17 +265,17 @@ __global__ void __launch_bounds__(32 * WPC, MINB) render_bwd_kernel(const uint2*
             const float2 inv = make_float2(rcp_approx_ftz(oma.x), rcp_approx_ftz(oma.y));
             T = mul2(T, inv);
             const float2 dch = mul2(alpha, T);
-            const float2 oml = sub2(bc2(1.0f), last_alpha);
-            ar0 = fma2(last_alpha, bc2(lc0), mul2(oml, ar0));
-            ar1 = fma2(last_alpha, bc2(lc1), mul2(oml, ar1));
-            ar2 = fma2(last_alpha, bc2(lc2), mul2(oml, ar2));
-            lc0 = b.w; lc1 = gb.x; lc2 = gb.y;
-            float2 dLa = mul2(sub2(bc2(lc0), ar0), dp0);
-            dLa = fma2(sub2(bc2(lc1), ar1), dp1, dLa);
-            dLa = fma2(sub2(bc2(lc2), ar2), dp2, dLa);
+            // backward.cu:545-556 with the three colour channels collapsed BEFORE the recurrence: the reference keeps
+            // accum_rec[c] (colour accumulated behind this Gaussian) per channel and forms sum_c (c_c - accum_rec[c]) dL/dpix_c;
+            // the recurrence is linear, so A = sum_c accum_rec[c] dL/dpix_c obeys the same one with D = colour . dL/dpix in
+            // place of the colour: 8 FP32 operations per pixel instead of 14 (the kernel is co-bound by the FP32 pipes).
+            A = fma2(last_alpha, Dl, mul2(last_oma, A));
+            Dl = fma2(bc2(gb.y), dp2, fma2(bc2(gb.x), dp1, mul2(bc2(b.w), dp0)));
             last_alpha = alpha;
-            dLa = fma2(inv, nTfbg, mul2(dLa, T));
-            const float2 w = mul2(mul2(bc2(b.z), dLa), G);
+            last_oma = oma;
+            const float2 dLa = mul2(sub2(Dl, A), T);
+            // w = G dL/dalpha WITHOUT the opacity factor: phase 2 scales the five moments by it once per Gaussian
+            const float2 w = mul2(dLa, G);
             sts128<0>(myrow + (uint32_t)ns * 16, make_float4(w.x, w.y, dch.x, dch.y));
             if (lane == 0) sts128<WP_SLOTS + SL_INFO>(wbuf + (uint32_t)ns * SL_ROW, make_float4(a.x, a.y, b.z, __uint_as_float(gid)));
             if (++ns == NS) {
@@ -318,16 +316,13 @@ void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2*
     static const int variant = [] { const char* e = getenv("GSR_RB_VARIANT"); return e ? atoi(e) : 0; }();
 #define GSR_RB_ARGS n_blocks, st, dev, ranges, point_list, W, H, grid_x, row_begin, packed, bg, final_T, n_contrib, dL_dpix, grad_acc, warp_mask
     switch (variant) {
-        case 1: launch_variant<16, 4, 4>(GSR_RB_ARGS); break;
-        case 2: launch_variant<8, 4, 6>(GSR_RB_ARGS); break;
-        case 3: launch_variant<8, 4, 7>(GSR_RB_ARGS); break;
-        case 4: launch_variant<16, 1, 16>(GSR_RB_ARGS); break;
-        case 5: launch_variant<16, 1, 20>(GSR_RB_ARGS); break;
-        case 6: launch_variant<8, 1, 24>(GSR_RB_ARGS); break;
-        case 7: launch_variant<8, 1, 28>(GSR_RB_ARGS); break;
-        case 8: launch_variant<8, 2, 12>(GSR_RB_ARGS); break;
-        case 9: launch_variant<16, 2, 8>(GSR_RB_ARGS); break;
-        default: launch_variant<8, 1, 20>(GSR_RB_ARGS); break;      // measured best at C2 (0.968 ms), see profiles/r02_sweep_rb_*.log
+        case 1: launch_variant<8, 4, 6>(GSR_RB_ARGS); break;
+        case 2: launch_variant<8, 4, 7>(GSR_RB_ARGS); break;
+        case 3: launch_variant<8, 1, 20>(GSR_RB_ARGS); break;
+        case 4: launch_variant<8, 1, 28>(GSR_RB_ARGS); break;
+        case 5: launch_variant<8, 2, 12>(GSR_RB_ARGS); break;
+        case 6: launch_variant<8, 1, 16>(GSR_RB_ARGS); break;
+        default: launch_variant<8, 1, 24>(GSR_RB_ARGS); break;      // measured best at C2 (0.809 ms), see profiles/r02_sweep_rb_*.log
     }
 #undef GSR_RB_ARGS
     count_launch(1);
