@@ -12,6 +12,7 @@
 //   * the depth-sort key/value pair is emitted here.
 #include "gsr_internal.cuh"
 #include "gsr_math.cuh"
+#include "gsr_smem.cuh"
 #include "gsr_fused_params.cuh"
 #include <stdio.h>
 
@@ -90,6 +91,13 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
     // in_frustum (auxiliary.h:144-175): only the near-plane test is live
     const float depth = dot4(V[2], V[6], V[10], V[14], mx, my, mz);
     bool alive = in_range && !(depth <= 0.2f);
+    // The SH row is needed only after the whole projection has been computed (a second dependent memory round trip): ask L2
+    // for its two 128-byte lines now.  A fifth of these rows belong to Gaussians that turn out to be off-screen.
+    if (alive && !SPLIT && a.colors_precomp == nullptr) {
+        const char* row = reinterpret_cast<const char*>(a.shs + (size_t)idx * a.M * 3);
+        prefetch_l2(row);
+        if (a.M * 12 > 128) prefetch_l2(row + 128);
+    }
     if (in_range && !alive && a.prefiltered) {
         printf("Point is filtered although prefiltered is set. This shouldn't happen!");
         __trap();
