@@ -581,6 +581,7 @@ int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* 
     if (!peer_blocks || !means3D || !dL_dsh) return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
     MultiviewShArgs a;
     a.P = P; a.D = D; a.M = M; a.n_views = n_views; a.means3D = means3D; a.dL_dsh = dL_dsh; a.begin = 0;
+    a.campos = nullptr; a.no_split = 0;
     for (int v = 0; v < 16; v++) a.blocks[v] = nullptr;
     for (int v = 0; v < n_views; v++) {
         if (!peer_blocks[v] || ((size_t)peer_blocks[v] & 15)) return fail(GSR_ERR_INVALID_ARGUMENT, "peer block missing or not 16-byte aligned");
@@ -590,6 +591,27 @@ int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* 
     cudaStream_t st = (cudaStream_t)cuda_stream;
     launch_multiview_sh_grad(a, st);
     GSR_STAGE("multiview sh grad", st, 0);
+    return GSR_OK;
+}
+
+int gsr_multiview_sh_grad_range(int begin, int end, int D, int M, int n_views, const float* const* peer_blocks, const float* campos,
+                                const float* means3D, float* dL_dsh, void* cuda_stream) {
+    if (begin < 0 || end < begin || (begin & 127) || D < 0 || D > 3 || M < (D + 1) * (D + 1) || n_views < 1 || n_views > GSR_MAX_VIEWS)
+        return fail(GSR_ERR_INVALID_ARGUMENT, "bad sizes (begin must be a multiple of 128)");
+    if (end == begin) return GSR_OK;
+    if (!peer_blocks || !campos || !means3D || !dL_dsh) return fail(GSR_ERR_INVALID_ARGUMENT, "null pointer");
+    MultiviewShArgs a;
+    a.P = end; a.D = D; a.M = M; a.n_views = n_views; a.means3D = means3D; a.dL_dsh = dL_dsh; a.begin = begin;
+    a.campos = campos; a.no_split = 1;
+    for (int v = 0; v < 16; v++) a.blocks[v] = nullptr;
+    for (int v = 0; v < n_views; v++) {
+        if (!peer_blocks[v] || ((size_t)peer_blocks[v] & 15)) return fail(GSR_ERR_INVALID_ARGUMENT, "peer block missing or not 16-byte aligned");
+        a.blocks[v] = peer_blocks[v];
+    }
+    if ((size_t)dL_dsh & 15) return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dsh not 16-byte aligned");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_multiview_sh_grad(a, st);
+    GSR_STAGE("multiview sh grad (range)", st, 0);
     return GSR_OK;
 }
 

@@ -210,6 +210,8 @@ struct MultiviewShArgs {
     const float* means3D;
     float* dL_dsh;
     int begin;                 // first Gaussian of this launch (chunked launches); P is the end bound
+    const float* campos;       // optional (n_views,4): camera positions; nullptr = the first 4 floats of each block
+    int no_split;              // 1 = one launch for [begin, P) (the caller pipelines ranges itself)
 };
 void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st);
 

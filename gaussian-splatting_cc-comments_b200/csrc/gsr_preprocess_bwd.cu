@@ -582,7 +582,7 @@ __global__ void __launch_bounds__(MV) multiview_sh_grad_kernel(MultiviewShArgs a
     const int row0 = a.begin + blockIdx.x * MV;
     const int nrows = min(MV, a.P - row0);
     const int t = threadIdx.x;
-    if (t < a.n_views * 4) s_campos[t] = a.blocks[t >> 2][t & 3];
+    if (t < a.n_views * 4) s_campos[t] = a.campos ? a.campos[t] : a.blocks[t >> 2][t & 3];
     // ---- peer loads: each view's (nrows,3) slice is one contiguous span ----
     const int n = nrows * 3, n4 = n >> 2;
     for (int v = 0; v < a.n_views; v++) {
@@ -645,7 +645,8 @@ __global__ void __launch_bounds__(256) multiview_sh_grad_kernel_generic(Multivie
         const float* blk = a.blocks[v];
         const float r = blk[4 + i3], g = blk[4 + i3 + 1], b = blk[4 + i3 + 2];
         if (r == 0.f && g == 0.f && b == 0.f) continue;
-        const float dx = subr(mx, blk[0]), dy = subr(my, blk[1]), dz = subr(mz, blk[2]);
+        const float* cp = a.campos ? a.campos + 4 * v : blk;
+        const float dx = subr(mx, cp[0]), dy = subr(my, cp[1]), dz = subr(mz, cp[2]);
         const float len = __fsqrt_rn(fmar(dz, dz, fmar(dx, dx, mulr(dy, dy))));
         float k[16];
         sh_basis(a.D, __fdiv_rn(dx, len), __fdiv_rn(dy, len), __fdiv_rn(dz, len), k);
@@ -713,7 +714,8 @@ void launch_multiview_sh_grad(const MultiviewShArgs& a, cudaStream_t st) {
     const size_t dyn = ((size_t)a.n_views * MV * 3 + (size_t)MV * S) * sizeof(float);
     // runs beside the all-reduce of the small gradients: chunked, see chunk_plan
     int bounds[5];
-    const int nchunk = chunk_plan(a.P, 256, bounds);
+    int nchunk = chunk_plan(a.P, 256, bounds);
+    if (a.no_split) { nchunk = 1; bounds[0] = a.begin; bounds[1] = a.P; }
     for (int c = 0; c < nchunk; c++) {
         MultiviewShArgs ac = a;
         ac.begin = bounds[c]; ac.P = bounds[c + 1];

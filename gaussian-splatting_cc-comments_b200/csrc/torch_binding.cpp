@@ -288,6 +288,21 @@ void multiviewShGrad(const std::vector<int64_t>& peer_ptrs, const torch::Tensor&
                                 dL_dsh.data_ptr<float>(), (void*)st));
 }
 
+// One range of Gaussians of the same exchange (gsr_multiview_sh_grad_range): block pointers may be virtual bases.
+void multiviewShGradRange(const std::vector<int64_t>& peer_ptrs, const torch::Tensor& campos, const torch::Tensor& means3D, torch::Tensor& dL_dsh,
+                          const int degree, const int64_t begin, const int64_t end) {
+    TORCH_CHECK(means3D.is_cuda() && dL_dsh.is_cuda() && dL_dsh.is_contiguous() && dL_dsh.dim() == 3, "bad tensors");
+    TORCH_CHECK(campos.is_cuda() && campos.is_contiguous() && campos.scalar_type() == torch::kFloat32 && campos.numel() >= 4 * (int64_t)peer_ptrs.size(),
+                "campos must be a contiguous CUDA float32 (n_views,4) tensor");
+    const c10::cuda::CUDAGuard guard(means3D.device());
+    std::vector<const float*> ptrs;
+    for (auto p : peer_ptrs) ptrs.push_back(reinterpret_cast<const float*>(p));
+    auto m3 = means3D.contiguous();
+    cudaStream_t st = c10::cuda::getCurrentCUDAStream(means3D.device().index()).stream();
+    check(gsr_multiview_sh_grad_range((int)begin, (int)end, degree, (int)dL_dsh.size(1), (int)ptrs.size(), ptrs.data(), campos.data_ptr<float>(),
+                                      m3.data_ptr<float>(), dL_dsh.data_ptr<float>(), (void*)st));
+}
+
 // introspection for the parity tests: (point_list, ranges, n_contrib, final_T, packed, tiles_touched, clamped) as tensors
 std::vector<torch::Tensor> viewBuffers(int P, int R, int W, int H, const torch::Tensor& geomBuffer,
                                        const torch::Tensor& binningBuffer, const torch::Tensor& imgBuffer) {
@@ -526,6 +541,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         return std::vector<int64_t>(b, b + n + 1);
     }, "Gaussian ranges of the chunked per-Gaussian backward (include/gsr.h: gsr_backward_chunk_plan)");
     m.def("multiview_sh_grad", &multiviewShGrad);
+    m.def("multiview_sh_grad_range", &multiviewShGradRange);
     m.def("mark_visible", &markVisible);
     m.def("view_buffers", &viewBuffers);
 }

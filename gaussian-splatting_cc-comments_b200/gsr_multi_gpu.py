@@ -201,6 +201,18 @@ def exchange_block_floats(P: int) -> int:
     return (4 + 3 * int(P) + 3) & ~3
 
 
+def exchange_chunks(P: int, n: int) -> List[Tuple[int, int]]:
+    """Ranges [begin, end) of Gaussians for the pipelined exchange: n ranges (fewer for small P), every begin a multiple of 128
+    (the SH kernel's row block; it also keeps every range's float offset a multiple of 4)."""
+    P, n = int(P), max(int(n), 1)
+    step = ((P + n - 1) // n + 127) // 128 * 128
+    out, b = [], 0
+    while b < P:
+        out.append((b, min(b + step, P)))
+        b += step
+    return out or [(0, 0)]
+
+
 class MultiViewExchange:
     """Gradient exchange for multi-view training: `views_per_rank` cameras per rank and step (SURVEY.md 8(e), C5:
     8 cameras per step = 8/4/2/1 views per GPU at 1/2/4/8 GPUs).
@@ -259,6 +271,14 @@ class MultiViewExchange:
         # GSR_MV_TIMELINE=1: timed events around every phase of the exchange (diagnostics; see timeline_report)
         self._tl = [] if os.environ.get("GSR_MV_TIMELINE") == "1" else None
         self._tl_cur = None
+        # "allgather" mode, GSR_MV_AG_CHUNKS = n > 1: the blocks travel in n ranges of Gaussians and each range's SH rows are
+        # written while the next range is still on the links.  Built, correct (2-GPU test) and measured SLOWER on 8 B200
+        # (3.75 ms per step with 4 ranges, 3.81 with 8, against 3.36 with one all-gather, profiles/r02_multigpu.md): the step
+        # is link-bound from the publish point on, smaller messages use the links less well, and the early SH kernels take
+        # SMs and HBM bandwidth from the per-Gaussian backward that gates the all-reduce.  Default: one all-gather.
+        self.ag_chunks = int(os.environ.get("GSR_MV_AG_CHUNKS", "1"))
+        self.campos_local = torch.zeros(self.views_per_rank, 4, dtype=torch.float32, device=self.device)
+        self.campos_all = torch.zeros(self.world * self.views_per_rank, 4, dtype=torch.float32, device=self.device)
         self._view = 0                  # local views whose backward has run in the current step
         self._pending_done = False      # the SH kernel of this step is still running on the side stream
         self._alloc(int(capacity))
@@ -309,7 +329,7 @@ class MultiViewExchange:
         self.small_mode = "multimem" if self.pack_mc else "nccl"
         if self.mode == "allgather":
             self.block = torch.zeros(n, dtype=torch.float32, device=self.device)
-            self.stage = torch.zeros(self.world * n, dtype=torch.float32, device=self.device)
+            self.stage = torch.zeros(self.world * (n + 64 * self.views_per_rank), dtype=torch.float32, device=self.device)
             self.handle, self.peer_ptrs = None, None
         else:
             self.block = self._symm.empty(n, dtype=torch.float32, device=self.device)
@@ -330,6 +350,7 @@ class MultiViewExchange:
         nb = exchange_block_floats(P)
         blk = self.block[self._view * nb:(self._view + 1) * nb]
         blk[:3].copy_(campos.reshape(-1)[:3], non_blocking=True)
+        self.campos_local[self._view, :3].copy_(campos.reshape(-1)[:3], non_blocking=True)
         last = self._view == self.views_per_rank - 1
         if self._tl is not None and last:
             self._tl_cur = []
@@ -355,7 +376,38 @@ class MultiViewExchange:
         self.side.wait_event(self.ev_drgb)
         with torch.cuda.stream(self.side):
             self._mark("drgb_published", self.side)
-            if self.mode == "allgather":
+            if self.mode == "allgather" and self.ag_chunks > 1 and P >= 4096:
+                # pipelined: the camera positions first (tiny), then per range of Gaussians and local view one all-gather, all
+                # queued at once from the comm stream (NCCL runs them in order); the side stream writes each range's SH rows
+                # as soon as that range has arrived, while the next range is on the links.
+                k = self.views_per_rank
+                chunks = exchange_chunks(P, self.ag_chunks)
+                self.comm.wait_event(self.ev_drgb)
+                works, bufs = [], []
+                with torch.cuda.stream(self.comm):
+                    dist.all_gather_into_tensor(self.campos_all.view(-1), self.campos_local.view(-1), group=self.group)
+                    off = 0
+                    for (b, e) in chunks:
+                        ln = (3 * (e - b) + 3) & ~3                      # floats per view of this range, 16-byte padded
+                        per_view = []
+                        for v in range(k):
+                            dst = self.stage[off: off + self.world * ln]
+                            src = self.block[v * nb + 4 + 3 * b: v * nb + 4 + 3 * b + ln]
+                            w = dist.all_gather_into_tensor(dst, src, group=self.group, async_op=True)
+                            per_view.append((dst, w))
+                            off += self.world * ln
+                        bufs.append((b, e, ln, per_view))
+                    self.ev_ag.record(self.comm)
+                # campos_all rows are in rank-major order (rank r, slot v) -> the same order as the pointers below
+                for ci, (b, e, ln, per_view) in enumerate(bufs):
+                    for _, w in per_view:
+                        w.wait()                                         # the side stream waits for this range only
+                    if ci == len(bufs) - 1:
+                        self._mark("allgather_done", self.side)
+                    ptrs = [per_view[v][0].data_ptr() + 4 * (r * ln) - 4 * (4 + 3 * b) for r in range(self.world) for v in range(k)]
+                    C.multiview_sh_grad_range(ptrs, self.campos_all, means3D, grad_sh, int(sh_degree), b, e)
+                self._mark("sh_kernel_done", self.side)
+            elif self.mode == "allgather":
                 out = self.stage[: self.world * n]
                 dist.all_gather_into_tensor(out, self.block[:n], group=self.group)
                 self.ev_ag.record(self.side)

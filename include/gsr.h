@@ -184,6 +184,13 @@ int gsr_backward(const gsr_backward_args* args, void* cuda_stream);
 int gsr_multiview_sh_grad(int P, int D, int M, int n_views, const float* const* peer_blocks, const float* means3D,
                           float* dL_dsh, void* cuda_stream);
 
+/* The same for Gaussians [begin, end) only (begin a multiple of 128), so that a caller can pipeline the exchange: gather the
+ * dL_drgb of one range of Gaussians from every rank while the previous range's dL_dsh rows are being written.  campos is a
+ * separate (n_views,4) array here; peer_blocks[v] + 4 + 3 i must be the address of view v's dL_drgb of Gaussian i for
+ * i in [begin, end) -- the pointer itself may be a VIRTUAL base in front of a buffer that holds only that range. */
+int gsr_multiview_sh_grad_range(int begin, int end, int D, int M, int n_views, const float* const* peer_blocks, const float* campos,
+                                const float* means3D, float* dL_dsh, void* cuda_stream);
+
 /* Rows [begin, end) of a (P,14) small_pack block -> the five gradient tensors (see gsr_backward_args.small_pack). */
 int gsr_unpack_small_grads(int begin, int end, const float* small_pack, float* dL_dmean3D, float* dL_dmean2D,
                            float* dL_dopacity, float* dL_dscale, float* dL_drot, void* cuda_stream);

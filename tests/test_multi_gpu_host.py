@@ -44,6 +44,11 @@ def test_band_pixel_rows_clip_to_image():
 
 
 def test_cameras_for_rank():
+    for P in (0, 1, 127, 128, 129, 4096, 40001, 3000000):
+        for n in (1, 3, 4):
+            ch = MG.exchange_chunks(P, n)
+            assert ch[0][0] == 0 and ch[-1][1] == P and all(b % 128 == 0 for b, _ in ch) and len(ch) <= max(n, 1)
+            assert all(ch[i][1] == ch[i + 1][0] for i in range(len(ch) - 1))
     assert MG.cameras_for_rank(8, 1, 4) == [1, 5]
     assert sorted(sum((MG.cameras_for_rank(8, r, 8) for r in range(8)), [])) == list(range(8))
 
@@ -72,6 +77,11 @@ def test_exchange_blocks_stay_16_byte_aligned_for_any_P():
     for P in list(range(0, 70)) + [40000, 40001, 40002, 40003, 2999999, 3000000, 3000001]:
         n = MG.exchange_block_floats(P)
         assert n % 4 == 0 and 4 + 3 * P <= n < 4 + 3 * P + 4
+    for P in (0, 1, 127, 128, 129, 4096, 40001, 3000000):
+        for n in (1, 3, 4):
+            ch = MG.exchange_chunks(P, n)
+            assert ch[0][0] == 0 and ch[-1][1] == P and all(b % 128 == 0 for b, _ in ch) and len(ch) <= max(n, 1)
+            assert all(ch[i][1] == ch[i + 1][0] for i in range(len(ch) - 1))
     assert MG.cameras_for_rank(8, 1, 4) == [1, 5] and MG.cameras_for_rank(8, 7, 8) == [7] and MG.cameras_for_rank(8, 0, 1) == list(range(8))
 
 

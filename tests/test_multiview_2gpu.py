@@ -34,11 +34,12 @@ def _worker(rank, world, port, q):
         errs = {}
         # bench.exchange_check: every rank computes every view locally (no exchange) -> the expected sum, then runs its own
         # views through the fused exchange twice.  One and two views per rank, both transports, odd P (block alignment).
-        for mode in ("allgather", "peer"):
+        for mode, chunks in (("allgather", 1), ("allgather", 4), ("peer", 1)):     # 4: the pipelined ranges (gsr_multiview_sh_grad_range)
             os.environ["GSR_MULTIVIEW_MODE"] = mode
+            os.environ["GSR_MV_AG_CHUNKS"] = str(chunks)
             for vpr in (1, 2):
                 r = B.exchange_check(mod, dev, rank, world, vpr, P=40001)
-                errs["%s/vpr%d" % (mode, vpr)] = r["max_rel_l2"]
+                errs["%s%d/vpr%d" % (mode, chunks, vpr)] = r["max_rel_l2"]
         q.put((rank, errs))
     finally:
         dist.destroy_process_group()
