@@ -196,8 +196,11 @@ class Gaussians:
         self.denom[update_filter] += 1
 
 
-def render(cam, g, rasterizer_module, bg, scaling_modifier=1.0):
-    """gaussian_renderer/__init__.py:19-127 for the default pipeline (SH evaluated and covariance built by the rasterizer)."""
+def render(cam, g, rasterizer_module, bg, scaling_modifier=1.0, raw=False):
+    """gaussian_renderer/__init__.py:19-127 for the default pipeline (SH evaluated and covariance built by the rasterizer).
+    raw=True (this package's rasterizer only): the model's RAW tensors go to GaussianRasterizer.forward_raw, which applies
+    sigmoid / exp / normalize and reads the split SH storage inside the per-Gaussian kernels -- no torch
+    activation kernels, no torch.cat, and autograd has nothing to run after the rasterizer's backward."""
     screenspace_points = torch.zeros_like(g.xyz, requires_grad=True) + 0
     try:
         screenspace_points.retain_grad()
@@ -208,6 +211,9 @@ def render(cam, g, rasterizer_module, bg, scaling_modifier=1.0):
         scale_modifier=scaling_modifier, viewmatrix=cam["viewmatrix_t"], projmatrix=cam["projmatrix_t"], sh_degree=g.sh_degree,
         campos=cam["campos_t"], prefiltered=False, debug=False)
     rasterizer = rasterizer_module.GaussianRasterizer(raster_settings=settings)
+    if raw:
+        image, radii = rasterizer.forward_raw(g.xyz, screenspace_points, g.f_dc, g.f_rest, g.opacity, g.scaling, g.rotation)
+        return {"render": image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii}
     image, radii = rasterizer(means3D=g.xyz, means2D=screenspace_points, shs=g.get_features, colors_precomp=None,
                               opacities=g.get_opacity, scales=g.get_scaling, rotations=g.get_rotation, cov3D_precomp=None)
     return {"render": image, "viewspace_points": screenspace_points, "visibility_filter": radii > 0, "radii": radii}
@@ -253,7 +259,7 @@ class Phase:
 
 
 def train(g, cams, targets, rasterizer_module, loss_fn, iterations, densify_from, densify_every, target_P, extent, bg,
-          timed=True, seed=0, on_densify=None):
+          timed=True, seed=0, on_densify=None, raw=False):
     """The loop of train.py:73-175 without logging / saving / GUI.  loss_fn(image, gt, lambda_dssim) -> loss tensor.
     Returns the per-iteration phase table [(P, [render+loss fwd ms, backward ms, stats+densify ms, optimizer ms])]."""
     gen = torch.Generator(device=g.device).manual_seed(seed)
@@ -266,7 +272,7 @@ def train(g, cams, targets, rasterizer_module, loss_fn, iterations, densify_from
         cam = cams[(iteration - 1) % len(cams)]
         gt = targets[(iteration - 1) % len(cams)]
         ph.start()
-        pkg = render(cam, g, rasterizer_module, bg)
+        pkg = render(cam, g, rasterizer_module, bg, raw=raw)
         loss = loss_fn(pkg["render"], gt, g.opt.lambda_dssim)
         ph.mark()
         loss.backward()

@@ -66,6 +66,8 @@ def parse_args(argv=None):
     ap.add_argument("--width", type=int, default=1920)
     ap.add_argument("--height", type=int, default=1080)
     ap.add_argument("--views", type=int, default=8)
+    ap.add_argument("--no-raw", action="store_true", help="b200 arm: activations and the SH concatenation as torch ops (the reference's "
+                    "route through GaussianRasterizer.forward) instead of the fused raw-parameter path")
     return ap.parse_args(argv)
 
 
@@ -106,6 +108,7 @@ def run(a):
     torch.cuda.synchronize()
     t0 = time.time()
     table = T.train(g, cams, targets, module, loss_fn, a.iterations, a.densify_from, a.densify_every, a.target, extent, bg,
+                    raw=(a.impl == "b200" and not a.no_raw),
                     on_densify=lambda it, p0, p1, thr, st: log.append({"iteration": it, "P_before": p0, "P_after": p1, "threshold": thr,
                                                                        "cloned": st[0], "split": st[1], "pruned": st[2]}))
     torch.cuda.synchronize()
@@ -117,6 +120,7 @@ def run(a):
         "impl": a.impl, "unit": "ms/iter", "higher_is_better": False, "data": "synthetic", "dtype": "f32",
         "config": {"workload": "c3-train-loop", "P0": a.P0, "P_target": a.target, "iterations": a.iterations, "views": a.views,
                    "densify_from": a.densify_from, "densify_every": a.densify_every,
+                   "raw_parameter_path": bool(a.impl == "b200" and not a.no_raw),
                    "threshold": "quantile schedule (see tools/c3_trainer.py), not the reference's fixed 0.0002"},
         "value": float(np.mean(plain)), "final_P": g.P, "wall_s": wall, "buckets": buckets, "densifications": log})
 
