@@ -607,11 +607,16 @@ def c3_record(impl):
     1080p, one GPU (tools/train_c3.py; 660 iterations, densification every 50 from iteration 60).  The b200 line also runs the
     reference arm (unmodified reference rasterizer + torch loss / Adam / densification) when oracle/_ref is there."""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import gc
     import train_c3
     import torch
+    gc.collect()
+    torch.cuda.empty_cache()          # the loop re-allocates at every densification: start from an empty caching allocator, as a
+    torch.cuda.synchronize()          # training process would (measured: 5.6 instead of 4.3 ms/iter on top of the C2 / C4 leftovers)
 
     def arm(name):
         r = train_c3.run(train_c3.parse_args(["--impl", name]))
+        gc.collect()
         torch.cuda.empty_cache()
         return {"ms_per_iter_mean": r["value"], "final_P": r["final_P"], "iterations": r["config"]["iterations"],
                 "ms_per_iter_by_P": [[b["P_from"], round(b["iter_ms"], 3)] for b in r["buckets"]],
