@@ -19,7 +19,7 @@ def test_roofline_block_reports_the_dominant_kernel_and_its_committed_ncu_figure
     t = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
     P, R = t["P"], t["num_rendered"]
     stage = {"preprocess": (0.17, 20), "depth_sort": (0.18, 20), "scan": (0.04, 20), "duplicate": (0.07, 20), "tile_sort": (0.25, 20),
-             "tile_ranges": (0.02, 20), "render": (0.78, 20), "bwd_zero": (0.03, 20), "render_bwd": (1.36, 20), "preprocess_bwd": (0.35, 20)}
+             "tile_ranges": (0.02, 20), "render": (0.71, 20), "bwd_zero": (0.03, 20), "render_bwd": (0.80, 20), "preprocess_bwd": (0.35, 20)}
     out = b.roofline_block(stage, P, R, 1920 * 1080, int(0.77 * P), 16, 6551.0, "measured", 20)
     rl = out["roofline"]
     assert rl["kernel"] == "render_bwd_kernel" and rl["bound"] in ("hbm", "tensor") and rl["unit"] == "GB/s"
