@@ -299,9 +299,11 @@ int gsr_backward(const gsr_backward_args* a, void* cuda_stream) {
         !a->viewmatrix || !a->projmatrix || !a->cam_pos || !a->background || !a->grad_scratch)
         return fail(GSR_ERR_INVALID_ARGUMENT, "missing required pointer");
     const bool split_sh = a->features_dc != nullptr;
-    if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dcolor || !a->dL_dmean3D || !a->dL_dcov3D || !a->dL_dscale || !a->dL_drot ||
-        (a->M > 0 && !split_sh && !a->dL_dsh))
+    if (!a->dL_dmean2D || !a->dL_dopacity || !a->dL_dmean3D || !a->dL_dscale || !a->dL_drot || (a->M > 0 && !split_sh && !a->dL_dsh))
         return fail(GSR_ERR_INVALID_ARGUMENT, "missing output pointer");
+    // the gradient of an input that was not given may be left out (NULL): 36 bytes per Gaussian less to write on the SH / scale+rotation path
+    if ((a->colors_precomp && !a->dL_dcolor) || (a->cov3D_precomp && !a->dL_dcov3D))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "dL_dcolor / dL_dcov3D are required when colors_precomp / cov3D_precomp are given");
     if (split_sh) {
         if (a->shs || a->dL_dsh || a->colors_precomp || a->M <= 0 || a->M > 16 || !a->dL_dfeatures_dc || (a->M > 1 && (!a->features_rest || !a->dL_dfeatures_rest)))
             return fail(GSR_ERR_INVALID_ARGUMENT, "split SH storage: features_dc/_rest with dL_dfeatures_dc/_rest, M <= 16, no shs / dL_dsh / colors_precomp");

@@ -362,9 +362,11 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
     const int sh_written = bwd_one<false, RAW, false>(a, idx, in, s_cam, s_cam + 16, a.shs ? a.shs + (size_t)idx * a.M * 3 : nullptr, dsh, o);
     // ---- write everything (zeros where the reference's pre-zeroed tensors stay untouched) ----
     if (a.dL_dconic) reinterpret_cast<float4*>(a.dL_dconic)[idx] = make_float4(o.g[2], o.g[3], 0.f, o.g[4]);
-    a.dL_dcolor[i3] = o.g[6]; a.dL_dcolor[i3 + 1] = o.g[7]; a.dL_dcolor[i3 + 2] = o.g[8];
+    if (a.dL_dcolor) { a.dL_dcolor[i3] = o.g[6]; a.dL_dcolor[i3 + 1] = o.g[7]; a.dL_dcolor[i3 + 2] = o.g[8]; }
+    if (a.dL_dcov3D) {
 #pragma unroll
-    for (int i = 0; i < 6; i++) a.dL_dcov3D[6 * (size_t)idx + i] = o.dcov[i];
+        for (int i = 0; i < 6; i++) a.dL_dcov3D[6 * (size_t)idx + i] = o.dcov[i];
+    }
     if (a.small_pack) {
         float* row = a.small_pack + 14 * (size_t)idx;
         row[0] = o.dmean[0]; row[1] = o.dmean[1]; row[2] = o.dmean[2];
@@ -491,8 +493,8 @@ __global__ void __launch_bounds__(PB, MINB) preprocess_bwd_kernel_staged(Preproc
     }
     __syncthreads();
     if (a.dL_dconic) copy_out(a.dL_dconic + (size_t)row0 * 4, s_out + 3 * PB, nrows * 4);
-    copy_out(a.dL_dcolor + (size_t)row0 * 3, s_out + 8 * PB, nrows * 3);
-    copy_out(a.dL_dcov3D + (size_t)row0 * 6, s_out + 14 * PB, nrows * 6);
+    if (a.dL_dcolor) copy_out(a.dL_dcolor + (size_t)row0 * 3, s_out + 8 * PB, nrows * 3);
+    if (a.dL_dcov3D) copy_out(a.dL_dcov3D + (size_t)row0 * 6, s_out + 14 * PB, nrows * 6);
     if (a.dL_drgb) copy_out(a.dL_drgb + (size_t)row0 * 3, s_out + 27 * PB, nrows * 3);
     if (pack) {
         copy_out(a.small_pack + (size_t)row0 * 14, s_out + 30 * PB, nrows * 14);

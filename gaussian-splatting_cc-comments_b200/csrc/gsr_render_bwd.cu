@@ -50,14 +50,14 @@ struct BwLayout {
     static constexpr int WP_BYTES = WP_DP + 32 * DP_ROW;
 };
 
-// Phase 2, one pixel column of the lane's two rows: raw moments about the block centre.  X = column - 3.5 (exact).
+// Phase 2, one pixel column of the lane's two rows: raw moments about the column c0 nearest to the Gaussian.  X = column - c0 (exact).
 template <int OFF_E, int OFF_D, int COL>
-__device__ __forceinline__ void phase2_col(const uint32_t base, const uint32_t dbase, float2& S, float2& Mx, float2& Mxx, float2& V6, float2& V7,
-                                           float2& V8) {
+__device__ __forceinline__ void phase2_col(const uint32_t base, const uint32_t dbase, const float c0, float2& S, float2& Mx, float2& Mxx, float2& V6,
+                                           float2& V7, float2& V8) {
     const float4 e = lds128<OFF_E>(base);
     const float2 d0 = lds64<OFF_D>(dbase), d1 = lds64<OFF_D + 8>(dbase), d2 = lds64<OFF_D + 16>(dbase);
     const float2 Wp = make_float2(e.x, e.y), Dc = make_float2(e.z, e.w);
-    constexpr float X = (float)COL - 3.5f;
+    const float X = (float)COL - c0;
     S = add2(S, Wp);
     Mx = fma2(Wp, bc2(X), Mx);
     Mxx = fma2(Wp, bc2(X * X), Mxx);
@@ -68,11 +68,12 @@ __device__ __forceinline__ void phase2_col(const uint32_t base, const uint32_t d
 
 // Phase 2: the nine sums of the n <= NS Gaussians parked in this warp's slots.  Warp-uniform call.  NS = 8:
 // lane (slot g = lane % 8, part h = lane / 8) walks the 8 pixel lanes of rows h and h + 4 of the block.  Per pixel only the
-// raw moments sum w, sum w x, sum w x^2 about the block centre are accumulated (x = column - 3.5 is a compile-time constant
-// and y is constant along a row); the moments about the Gaussian's centre the gradients need,
+// raw moments sum w, sum w x, sum w x^2 about a block column c0 are accumulated (x = column - c0 is one subtraction per column
+// and lane, y is constant along a row); the moments about the Gaussian's centre the gradients need,
 //     sum w dx = ax S - Mx,   sum w dx^2 = ax^2 S - 2 ax Mx + Mxx,   sum w dy = dy S,   sum w dx dy = dy (ax S - Mx),   sum w dy^2 = dy^2 S
-// with ax = x_gaussian - x_centre, follow once per lane (a Gaussian that reaches the block has |ax| <= 3.5 + 3.4 sigma_x, so the
-// shift cancels at most one digit).  6 packed FP32 operations per pixel pair instead of 11: the kernel is co-bound by the FP32 pipes.
+// with ax = x_gaussian - x_c0, follow once per lane.  c0 is the block column nearest to the Gaussian, so the shift does not
+// cancel (|ax| <= 1/2 when the centre is over the block; otherwise dx keeps one sign).  6 packed FP32 operations per pixel pair
+// instead of 11: the kernel is co-bound by the FP32 pipes.
 template <int NS>
 __device__ __forceinline__ void flush_slots(const uint32_t wbuf, const int n, const int lane, const float fx0, const float fy0,
                                             float* __restrict__ grad_acc) {
@@ -83,17 +84,20 @@ __device__ __forceinline__ void flush_slots(const uint32_t wbuf, const int n, co
     const float4 info = lds128<L::WP_SLOTS + L::SL_INFO>(wbuf + (uint32_t)g * L::SL_ROW);          // x, y, opacity, id
     const uint32_t base = wbuf + (uint32_t)(L::WP_SLOTS + h * 8 * L::SL_ROW + g * 16);
     const uint32_t dbase = wbuf + (uint32_t)(L::WP_DP + h * 8 * L::DP_ROW);
+    // x origin of the raw moments: the block column nearest to the Gaussian's centre.  With the centre inside the block's columns
+    // the shift below is at most half a pixel; outside, dx has one sign over the whole block: no cancellation either way.
+    const float c0 = rintf(fminf(fmaxf(subr(info.x, fx0), 0.0f), 7.0f));
     float2 S = make_float2(0.f, 0.f), Mx = S, Mxx = S, V6 = S, V7 = S, V8 = S;
-    phase2_col<0 * L::SL_ROW, 0 * L::DP_ROW, 0>(base, dbase, S, Mx, Mxx, V6, V7, V8);
-    phase2_col<1 * L::SL_ROW, 1 * L::DP_ROW, 1>(base, dbase, S, Mx, Mxx, V6, V7, V8);
-    phase2_col<2 * L::SL_ROW, 2 * L::DP_ROW, 2>(base, dbase, S, Mx, Mxx, V6, V7, V8);
-    phase2_col<3 * L::SL_ROW, 3 * L::DP_ROW, 3>(base, dbase, S, Mx, Mxx, V6, V7, V8);
-    phase2_col<4 * L::SL_ROW, 4 * L::DP_ROW, 4>(base, dbase, S, Mx, Mxx, V6, V7, V8);
-    phase2_col<5 * L::SL_ROW, 5 * L::DP_ROW, 5>(base, dbase, S, Mx, Mxx, V6, V7, V8);
-    phase2_col<6 * L::SL_ROW, 6 * L::DP_ROW, 6>(base, dbase, S, Mx, Mxx, V6, V7, V8);
-    phase2_col<7 * L::SL_ROW, 7 * L::DP_ROW, 7>(base, dbase, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<0 * L::SL_ROW, 0 * L::DP_ROW, 0>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<1 * L::SL_ROW, 1 * L::DP_ROW, 1>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<2 * L::SL_ROW, 2 * L::DP_ROW, 2>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<3 * L::SL_ROW, 3 * L::DP_ROW, 3>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<4 * L::SL_ROW, 4 * L::DP_ROW, 4>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<5 * L::SL_ROW, 5 * L::DP_ROW, 5>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<6 * L::SL_ROW, 6 * L::DP_ROW, 6>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
+    phase2_col<7 * L::SL_ROW, 7 * L::DP_ROW, 7>(base, dbase, c0, S, Mx, Mxx, V6, V7, V8);
     // shift to the Gaussian's centre (dx = x_g - x_pixel = ax - X, dy = y_g - y_row)
-    const float ax = subr(info.x, fx0 + 3.5f);
+    const float ax = subr(info.x, fx0 + c0);
     const float fyh = fy0 + (float)h;
     const float2 dy = make_float2(subr(info.y, fyh), subr(info.y, fyh + 4.0f));
     const float2 sdx = sub2(mul2(bc2(ax), S), Mx);                                   // sum w dx per row

@@ -101,14 +101,17 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
     // one flat gradient arena; per-Gaussian widths: mean2D 3 (never exchanged between ranks: densification takes per-view
     // norms), then mean3D 3, opacity 1, scale 3, rot 4 (the small live blocks, contiguous so that ONE all-reduce covers
     // them in multi-view training), sh 3M, then the blocks training never reads: colour 3, cov3D 6, conic 4
-    const int64_t widths[9] = {3, 3, 1, 3, 4, 3 * M, 3, 6, 4};
-    int64_t offs[10]; offs[0] = 0;
-    for (int i = 0; i < 9; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;   // keep 16-byte alignment
-    torch::Tensor flat = torch::empty({offs[9]}, fopt);
+    // Gradients of inputs that were not given (precomputed colours / covariances on the usual SH + scale/rotation path) and
+    // dL_dconic (never returned) are neither allocated nor written: 52 bytes per Gaussian less for the per-Gaussian backward.
+    const bool want_col = colors.numel() != 0, want_cov = cov3D_precomp.numel() != 0;
+    const int64_t widths[8] = {3, 3, 1, 3, 4, 3 * M, want_col ? 3 : 0, want_cov ? 6 : 0};
+    int64_t offs[9]; offs[0] = 0;
+    for (int i = 0; i < 8; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;   // keep 16-byte alignment
+    torch::Tensor flat = torch::empty({offs[8]}, fopt);
     auto view = [&](int i, std::vector<int64_t> shape) { return flat.narrow(0, offs[i], widths[i] * P).view(shape); };
     torch::Tensor dL_dmeans2D = view(0, {P, 3}), dL_dmeans3D = view(1, {P, 3}), dL_dopacity = view(2, {P, 1}),
                   dL_dscales = view(3, {P, 3}), dL_drotations = view(4, {P, 4}), dL_dsh = view(5, {P, M, 3}),
-                  dL_dcolors = view(6, {P, 3}), dL_dcov3D = view(7, {P, 6}), dL_dconic = view(8, {P, 2, 2});
+                  dL_dcolors = want_col ? view(6, {P, 3}) : torch::empty({0}, fopt), dL_dcov3D = want_cov ? view(7, {P, 6}) : torch::empty({0}, fopt);
     if (P != 0) {
         auto bg = prep(background, dev, "bg"), m3 = prep(means3D, dev, "means3D"), col = prep(colors, dev, "colors_precomp"),
              sc = prep(scales, dev, "scales"), rot = prep(rotations, dev, "rotations"), cov = prep(cov3D_precomp, dev, "cov3D_precomp"),
@@ -128,9 +131,9 @@ RasterizeGaussiansBackwardCUDA(const torch::Tensor& background, const torch::Ten
         a.binning_buffer = reinterpret_cast<const char*>(binningBuffer.data_ptr());
         a.image_buffer = reinterpret_cast<const char*>(imageBuffer.data_ptr());
         a.dL_dpix = fptr(dpix);
-        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dconic = dL_dconic.data_ptr<float>();
-        a.dL_dopacity = dL_dopacity.data_ptr<float>(); a.dL_dcolor = dL_dcolors.data_ptr<float>();
-        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dcov3D = dL_dcov3D.data_ptr<float>();
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dconic = nullptr;
+        a.dL_dopacity = dL_dopacity.data_ptr<float>(); a.dL_dcolor = want_col ? dL_dcolors.data_ptr<float>() : nullptr;
+        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dcov3D = want_cov ? dL_dcov3D.data_ptr<float>() : nullptr;
         a.dL_dsh = M > 0 ? dL_dsh.data_ptr<float>() : nullptr;
         a.dL_dscale = dL_dscales.data_ptr<float>(); a.dL_drot = dL_drotations.data_ptr<float>();
         a.grad_scratch = reinterpret_cast<float*>(scratch.data_ptr());
@@ -221,14 +224,15 @@ RasterizeGaussiansRawBackwardCUDA(const torch::Tensor& background, const torch::
     const int64_t Mr = features_rest.size(1);
     auto fopt = means3D.options().dtype(torch::kFloat32);
     // one flat arena as in rasterize_gaussians_backward: the live blocks first, then the ones training never reads
-    const int64_t widths[10] = {3, 3, 1, 3, 4, 3, 3 * Mr, 3, 6, 4};
-    int64_t offs[11]; offs[0] = 0;
-    for (int i = 0; i < 10; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;
-    torch::Tensor flat = torch::empty({offs[10]}, fopt);
+    // (the gradients of precomputed colours / covariances and dL_dconic have no reader on this path: not allocated, not written)
+    const int64_t widths[7] = {3, 3, 1, 3, 4, 3, 3 * Mr};
+    int64_t offs[8]; offs[0] = 0;
+    for (int i = 0; i < 7; i++) offs[i + 1] = offs[i] + ((widths[i] * P + 3) / 4) * 4;
+    torch::Tensor flat = torch::empty({offs[7]}, fopt);
     auto view = [&](int i, std::vector<int64_t> shape) { return flat.narrow(0, offs[i], widths[i] * P).view(shape); };
     torch::Tensor dL_dmeans3D = view(0, {P, 3}), dL_dmeans2D = view(1, {P, 3}), dL_dopacity = view(2, {P, 1}),
                   dL_dscales = view(3, {P, 3}), dL_drotations = view(4, {P, 4}), dL_ddc = view(5, {P, 1, 3}),
-                  dL_drest = view(6, {P, Mr, 3}), dL_dcolors = view(7, {P, 3}), dL_dcov3D = view(8, {P, 6}), dL_dconic = view(9, {P, 2, 2});
+                  dL_drest = view(6, {P, Mr, 3});
     if (P != 0) {
         auto bg = prep(background, dev, "bg"), m3 = prep(means3D, dev, "means3D"), dc = prep(features_dc, dev, "features_dc"),
              rest = prep(features_rest, dev, "features_rest"), sc = prep(raw_scaling, dev, "scaling"), rot = prep(raw_rotation, dev, "rotation"),
@@ -247,9 +251,9 @@ RasterizeGaussiansRawBackwardCUDA(const torch::Tensor& background, const torch::
         a.binning_buffer = reinterpret_cast<const char*>(binningBuffer.data_ptr());
         a.image_buffer = reinterpret_cast<const char*>(imageBuffer.data_ptr());
         a.dL_dpix = fptr(dpix);
-        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dconic = dL_dconic.data_ptr<float>();
-        a.dL_dopacity = dL_dopacity.data_ptr<float>(); a.dL_dcolor = dL_dcolors.data_ptr<float>();
-        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dcov3D = dL_dcov3D.data_ptr<float>();
+        a.dL_dmean2D = dL_dmeans2D.data_ptr<float>(); a.dL_dconic = nullptr;
+        a.dL_dopacity = dL_dopacity.data_ptr<float>(); a.dL_dcolor = nullptr;
+        a.dL_dmean3D = dL_dmeans3D.data_ptr<float>(); a.dL_dcov3D = nullptr;
         a.dL_dscale = dL_dscales.data_ptr<float>(); a.dL_drot = dL_drotations.data_ptr<float>();
         a.grad_scratch = reinterpret_cast<float*>(scratch.data_ptr());
         a.debug = debug;

@@ -107,9 +107,9 @@ typedef struct gsr_backward_args {
     float* dL_dmean2D;           /* (P,3) */
     float* dL_dconic;            /* (P,4) = (P,2,2), may be NULL (the reference does not return it) */
     float* dL_dopacity;          /* (P,1) */
-    float* dL_dcolor;            /* (P,3) */
+    float* dL_dcolor;            /* (P,3); may be NULL when colors_precomp is NULL (then nobody reads it) */
     float* dL_dmean3D;           /* (P,3) */
-    float* dL_dcov3D;            /* (P,6) */
+    float* dL_dcov3D;            /* (P,6); may be NULL when cov3D_precomp is NULL */
     float* dL_dsh;               /* (P,M,3), NULL iff M == 0 */
     float* dL_dscale;            /* (P,3) */
     float* dL_drot;              /* (P,4) */
