@@ -211,6 +211,8 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     pa.depth_keys = geom.keys[0]; pa.ids = geom.vals[0];
     pa.total = geom.total;
     pa.raw_act = a->raw_activations ? 1 : 0; pa.f_dc = a->features_dc; pa.f_rest = a->features_rest;
+    const bool use_rects = grid_x < 65536 && grid_y < 65536;      // 16-bit tile coordinates in the packed rectangle
+    pa.rects = use_rects ? geom.rects : nullptr;
     GSR_CUDA(cudaMemsetAsync(geom.total, 0, sizeof(uint32_t), st));
     { StageTimer t(ST_PREPROCESS, st); launch_preprocess(pa, st); }
     GSR_STAGE("preprocess", st, a->debug);
@@ -242,7 +244,8 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     {
         StageTimer t(ST_SCAN, st);
         // (a single-pass gather + scan with decoupled look-back measured slower here: 0.044 vs 0.036 ms at P = 3 M)
-        launch_gather_u32(geom.tiles_touched, geom.vals[0], geom.tt_sorted, P, st);
+        if (use_rects) launch_gather_tt_rect(geom.tiles_touched, geom.rects, geom.vals[0], geom.tt_sorted, geom.rect_sorted, P, st);
+        else launch_gather_u32(geom.tiles_touched, geom.vals[0], geom.tt_sorted, P, st);
         scan_exclusive_u32(geom.tt_sorted, geom.offsets, P, geom.scan_tmp, nullptr, st);
     }
     GSR_STAGE("scan", st, a->debug);
@@ -260,7 +263,8 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     int s = npass & 1;       // start so that the last pass lands in vals[0] == point_list
     {
         StageTimer t(ST_DUPLICATE, st);
-        launch_duplicate(P, geom.vals[0], geom.offsets, geom.tt_sorted, geom.packed, radii, grid_x, grid_y, row_begin, row_end,
+        launch_duplicate(P, geom.vals[0], geom.offsets, geom.tt_sorted, use_rects ? geom.rect_sorted : nullptr, geom.packed, radii, grid_x, grid_y,
+                         row_begin, row_end,
                          bin.keys[s], bin.vals[s], st);
     }
     GSR_STAGE("duplicate", st, a->debug);

@@ -365,6 +365,24 @@ void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, 
     count_launch(1);
 }
 
+// tiles_touched and the tile rectangle into depth order in one pass (the rectangle only for Gaussians that emit instances)
+__global__ void __launch_bounds__(256) gather_tt_rect_kernel(const uint32_t* __restrict__ tt, const uint2* __restrict__ rects,
+                                                             const uint32_t* __restrict__ idx, uint32_t* __restrict__ tt_sorted,
+                                                             uint2* __restrict__ rect_sorted, size_t n) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const uint32_t g = idx[i];
+    const uint32_t c = __ldg(tt + g);
+    tt_sorted[i] = c;
+    if (c) rect_sorted[i] = __ldg(rects + g);
+}
+void launch_gather_tt_rect(const uint32_t* tt, const uint2* rects, const uint32_t* idx, uint32_t* tt_sorted, uint2* rect_sorted, size_t n,
+                           cudaStream_t st) {
+    if (n == 0) return;
+    gather_tt_rect_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(tt, rects, idx, tt_sorted, rect_sorted, n);
+    count_launch(1);
+}
+
 // duplicateWithKeys (rasterizer_impl.cu:78-126), walked in depth order; key = tile id only.
 __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
                                                         const uint32_t* __restrict__ tt_sorted, const float4* __restrict__ packed,
@@ -392,10 +410,11 @@ __global__ void __launch_bounds__(256) duplicate_kernel(int P, const uint32_t* _
 // the prefix sum in this same order).  Lanes walk that span 32 entries at a time, find each entry's owner with
 // a 5-step shuffle search over the lanes' span starts, and write keys and ids fully coalesced; a Gaussian that
 // covers hundreds of tiles is spread over the warp instead of serialising one lane.
+// Everything it reads is sequential in depth order (id, offset, count, rectangle: 20 bytes per Gaussian); round 1 gathered the
+// 16-byte record and the radius per Gaussian here (361 MB of sector traffic for 156 MB of algorithmic bytes at C2).
 __global__ void __launch_bounds__(256) duplicate_coop_kernel(int P, const uint32_t* __restrict__ order, const uint32_t* __restrict__ offsets,
-                                                             const uint32_t* __restrict__ tt_sorted, const float4* __restrict__ packed,
-                                                             const int* __restrict__ radii, int grid_x, int grid_y, int row_begin, int row_end,
-                                                             uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ vals) {
+                                                             const uint32_t* __restrict__ tt_sorted, const uint2* __restrict__ rect_sorted,
+                                                             int grid_x, uint32_t* __restrict__ tile_keys, uint32_t* __restrict__ vals) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint32_t cnt = 0, g = 0, off = 0, xy0 = 0, w = 1;
@@ -404,12 +423,9 @@ __global__ void __launch_bounds__(256) duplicate_coop_kernel(int P, const uint32
         off = offsets[i];
         if (cnt != 0) {
             g = order[i];
-            const float4 a = __ldg(packed + 3 * (size_t)g);
-            uint32_t x0, y0, x1, y1;
-            get_rect(a.x, a.y, radii[g], (uint32_t)grid_x, (uint32_t)grid_y, x0, y0, x1, y1);
-            y0 = max(y0, (uint32_t)row_begin);
-            xy0 = x0 | (y0 << 16);
-            w = x1 - x0;
+            const uint2 rc = rect_sorted[i];
+            xy0 = rc.x;
+            w = rc.y;
         }
     }
     const uint32_t base = __shfl_sync(0xffffffffu, off, 0);
@@ -435,13 +451,12 @@ __global__ void __launch_bounds__(256) duplicate_coop_kernel(int P, const uint32
     }
 }
 
-void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, const uint32_t* tt_sorted,
+void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, const uint32_t* tt_sorted, const uint2* rect_sorted,
                       const float4* packed, const int* radii, int grid_x, int grid_y, int row_begin, int row_end,
                       uint32_t* tile_keys, uint32_t* vals, cudaStream_t st) {
     if (P <= 0) return;
-    if (grid_x < 65536 && grid_y < 65536)       // measured 0.111 -> 0.075 ms at C2 against the one-thread-per-Gaussian walk
-        duplicate_coop_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
-                                                               row_begin, row_end, tile_keys, vals);
+    if (grid_x < 65536 && grid_y < 65536 && rect_sorted != nullptr)   // measured 0.111 -> 0.075 ms at C2 against the one-thread-per-Gaussian walk
+        duplicate_coop_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, rect_sorted, grid_x, tile_keys, vals);
     else
         duplicate_kernel<<<(P + 255) / 256, 256, 0, st>>>(P, order, offsets, tt_sorted, packed, radii, grid_x, grid_y,
                                                           row_begin, row_end, tile_keys, vals);

@@ -56,6 +56,8 @@ struct GeomState {
     uint8_t* clamped;          // P
     uint32_t* keys[2];         // P each: depth bits (0xFFFFFFFF = emits nothing), ping-pong
     uint32_t* vals[2];         // P each: Gaussian ids, ping-pong
+    uint2* rects;              // P: (x0 | y0 << 16, width) of the band-clipped tile rectangle, for Gaussians that emit instances
+    uint2* rect_sorted;        // P: the same in depth order
     uint32_t* tt_sorted;       // P: tiles_touched in depth order
     uint32_t* offsets;         // P: exclusive scan of tt_sorted
     uint32_t* table;           // rs_blocks(P) * RS_BINS + 512 (digit histogram, ticket, look-back table)
@@ -70,6 +72,7 @@ struct GeomState {
         g.clamped = c.take<uint8_t>(P);
         g.keys[0] = c.take<uint32_t>(P); g.keys[1] = c.take<uint32_t>(P);
         g.vals[0] = c.take<uint32_t>(P); g.vals[1] = c.take<uint32_t>(P);
+        g.rects = c.take<uint2>(P); g.rect_sorted = c.take<uint2>(P);
         g.tt_sorted = c.take<uint32_t>(P);
         g.offsets = c.take<uint32_t>(P);
         size_t tbl = rs_table_words(P);
@@ -141,6 +144,7 @@ struct PreprocessArgs {
     int raw_act;               // opacities / scales / rotations are logits / log-scales / unnormalised quaternions
     const float* f_dc;         // (P,1,3) and
     const float* f_rest;       // (P,M-1,3): SH coefficients in split storage (then shs == nullptr)
+    uint2* rects;              // (x0 | y0 << 16, width) of the band-clipped tile rectangle of a Gaussian that emits instances
 };
 void launch_preprocess(const PreprocessArgs& a, cudaStream_t st);
 void launch_mark_visible(int P, const float* means, const float* view, unsigned char* present, cudaStream_t st);
@@ -154,8 +158,10 @@ void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, si
                     const int* bits, uint32_t* table, cudaStream_t st);
 
 void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, size_t n, cudaStream_t st);
+void launch_gather_tt_rect(const uint32_t* tt, const uint2* rects, const uint32_t* idx, uint32_t* tt_sorted, uint2* rect_sorted, size_t n,
+                           cudaStream_t st);
 
-void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, const uint32_t* tt_sorted,
+void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, const uint32_t* tt_sorted, const uint2* rect_sorted,
                       const float4* packed, const int* radii, int grid_x, int grid_y, int row_begin, int row_end,
                       uint32_t* tile_keys, uint32_t* vals, cudaStream_t st);
 

@@ -202,6 +202,8 @@ __global__ void __launch_bounds__(256, 4) preprocess_fwd_kernel(PreprocessArgs a
 
                 out_tiles = band_tiles;
                 out_key = __float_as_uint(depth);
+                // the duplicate stage reads this back in depth order (8 sequential bytes instead of gathering record and radius)
+                if (a.rects) a.rects[idx] = make_uint2(x0 | (by0 << 16), x1 - x0);
             } else if (out_radius != 0) {
                 // visible, but not in this rank's band: a neutral record (a banded backward reads it beside all-zero accumulators)
                 float4* rec = a.packed + 3 * (size_t)idx;

@@ -35,7 +35,7 @@ void emu_preprocess_fwd(int P, int D, int M, const float* means3D, const float* 
     std::vector<uint32_t> ids(P);
     a.ids = ids.data();
     *total = 0; a.total = total;
-    a.raw_act = raw_act; a.f_dc = f_dc; a.f_rest = f_rest;
+    a.raw_act = raw_act; a.f_dc = f_dc; a.f_rest = f_rest; a.rects = nullptr;
     const bool split = f_dc != nullptr;
     emu::launch(dim3((P + 255) / 256), dim3(256), [&] {
         if (!raw_act && !split) preprocess_fwd_kernel<false, false>(a);
