@@ -325,7 +325,7 @@ void launch_render_backward(int grid_x, int row_begin, int row_end, const uint2*
         case 3: launch_variant<8, 1, 20>(GSR_RB_ARGS); break;
         case 4: launch_variant<8, 1, 28>(GSR_RB_ARGS); break;
         case 5: launch_variant<8, 2, 12>(GSR_RB_ARGS); break;
-        case 6: launch_variant<8, 1, 16>(GSR_RB_ARGS); break;
+        case 6: launch_variant<8, 1, 32>(GSR_RB_ARGS); break;
         default: launch_variant<8, 1, 24>(GSR_RB_ARGS); break;      // measured best at C2 (0.809 ms), see profiles/r02_sweep_rb_*.log
     }
 #undef GSR_RB_ARGS
