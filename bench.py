@@ -233,13 +233,14 @@ def exchange_check(mod, device, rank, world, views_per_rank, P=40001, W=320, H=2
         for i in mine:
             e = float((views[i].means2D.grad - own2d[i]).norm() / own2d[i].norm().clamp_min(1e-30))
             errs["means2D_per_view"] = max(errs.get("means2D_per_view", 0.0), e)
+    transport = ex.mode
     MG.disable_multiview_training()
     worst = max(errs.values())
     t = torch.tensor([worst], device=device)
     torch.distributed.all_reduce(t, op=torch.distributed.ReduceOp.MAX)
     worst = float(t.item())
     return {"max_rel_l2": worst, "ok": bool(worst <= 1e-5), "bar": 1e-5, "views": n_views, "views_per_rank": views_per_rank,
-            "P": P, "image": "%dx%d" % (W, H), "per_tensor_rank0": {k: float("%.3g" % v) for k, v in errs.items()},
+            "P": P, "image": "%dx%d" % (W, H), "transport": transport, "per_tensor_rank0": {k: float("%.3g" % v) for k, v in errs.items()},
             "what": "fused exchange vs the sum of all views computed locally without exchange, two steps, max over ranks"}
 
 

@@ -388,6 +388,16 @@ int gsr_multimem_allreduce(void* multicast_base, size_t begin, size_t end, int r
     return GSR_OK;
 }
 
+int gsr_multimem_broadcast(void* multicast_dst, const float* src, size_t n_floats, void* cuda_stream) {
+    if (n_floats == 0) return GSR_OK;
+    if (!multicast_dst || !src || ((size_t)multicast_dst & 15) || ((size_t)src & 15) || (n_floats & 3))
+        return fail(GSR_ERR_INVALID_ARGUMENT, "multicast destination / source must be 16-byte aligned and the length a multiple of 4 floats");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    launch_multimem_broadcast((float*)multicast_dst, src, n_floats, 148 * 8, st);
+    GSR_STAGE("multimem broadcast", st, 0);
+    return GSR_OK;
+}
+
 size_t gsr_l1_ssim_scratch_floats(int planes, int height, int width) {
     if (planes <= 0 || height <= 0 || width <= 0) return 0;
     return 2 * l1_ssim_blocks(planes, height, width);

@@ -12,6 +12,7 @@
 // The caller brackets the launch with device barriers (every rank's rows written before; every slice broadcast
 // after).
 #include "gsr_internal.cuh"
+#include <cstdlib>
 
 namespace gsr {
 
@@ -54,6 +55,37 @@ __global__ void __launch_bounds__(MM_THREADS) multimem_allreduce_kernel(float* _
         const size_t t = t0 + threadIdx.x;
         if (t < t1) mm_st_f32(mc + t, mm_ld_reduce_f32(mc + t));
     }
+}
+
+// One rank's contribution to an all-gather done by the switch: n4 16-byte words from local memory are stored once to the
+// multicast address and land in EVERY rank's copy of the symmetric buffer (this rank's included).  Stores are fire-and-forget;
+// four independent loads per thread keep the local read side busy.
+__global__ void __launch_bounds__(256) multimem_broadcast_kernel(float* __restrict__ mc, const float4* __restrict__ src, size_t n4) {
+    const size_t stride = (size_t)gridDim.x * 256;
+    size_t i = (size_t)blockIdx.x * 256 + threadIdx.x;
+    for (; i + 3 * stride < n4; i += 4 * stride) {
+        const float4 a = __ldg(src + i), b = __ldg(src + i + stride), c = __ldg(src + i + 2 * stride), d = __ldg(src + i + 3 * stride);
+        mm_st_v4(mc + 4 * i, a);
+        mm_st_v4(mc + 4 * (i + stride), b);
+        mm_st_v4(mc + 4 * (i + 2 * stride), c);
+        mm_st_v4(mc + 4 * (i + 3 * stride), d);
+    }
+    for (; i < n4; i += stride) mm_st_v4(mc + 4 * i, __ldg(src + i));
+    __threadfence_system();      // the barrier kernel that follows on the stream signals the peers: order the stores before it
+}
+
+void launch_multimem_broadcast(float* mc_dst, const float* src, size_t n_floats, int max_blocks, cudaStream_t st) {
+    const size_t n4 = n_floats / 4;
+    if (n4 == 0) return;
+    // Few CTAs: the stores are bounded by the NVLink port, not by SMs, and this kernel runs beside the per-Gaussian backward
+    // (GSR_MC_BLOCKS overrides for sweeps).
+    static const int env_blocks = [] { const char* e = getenv("GSR_MC_BLOCKS"); return e ? atoi(e) : 0; }();
+    if (env_blocks > 0) max_blocks = env_blocks;
+    size_t need = (n4 + 1023) / 1024;
+    if (need < 1) need = 1;
+    const unsigned grid = (unsigned)(need < (size_t)max_blocks ? need : (size_t)max_blocks);
+    multimem_broadcast_kernel<<<grid, 256, 0, st>>>(mc_dst, reinterpret_cast<const float4*>(src), n4);
+    count_launch(1);
 }
 
 void launch_multimem_allreduce(float* mc_base, size_t begin, size_t end, int rank, int world, int max_blocks, cudaStream_t st) {

@@ -203,6 +203,7 @@ void launch_l1_ssim_forward(const float* img, const float* gt, int planes, int H
 void launch_l1_ssim_backward(const float* img, const float* gt, const float* dm_maps, int planes, int H, int W, float coef_l1,
                              float coef_ssim, const float* grad_out, float* dimg, cudaStream_t st);
 void launch_multimem_allreduce(float* mc_base, size_t begin, size_t end, int rank, int world, int max_blocks, cudaStream_t st);
+void launch_multimem_broadcast(float* mc_dst, const float* src, size_t n_floats, int max_blocks, cudaStream_t st);
 void launch_unpack_small(int begin, int end, const float* pack, float* dmean3D, float* dmean2D, float* dop, float* dscale,
                          float* drot, cudaStream_t st);
 void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st);

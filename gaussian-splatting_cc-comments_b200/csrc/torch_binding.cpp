@@ -364,6 +364,12 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         cudaStream_t st = c10::cuda::getCurrentCUDAStream((c10::DeviceIndex)device).stream();
         check(gsr_multimem_allreduce(reinterpret_cast<void*>(mc_ptr), (size_t)begin, (size_t)end, (int)rank, (int)world, (void*)st));
     }, "two-shot all-reduce of floats [begin,end) through an NVLS multicast address (include/gsr.h)");
+    m.def("multimem_broadcast", [](int64_t mc_dst_ptr, const torch::Tensor& src, int64_t n_floats) {
+        TORCH_CHECK(src.is_cuda() && src.is_contiguous() && src.scalar_type() == torch::kFloat32 && src.numel() >= n_floats, "src: contiguous CUDA float32");
+        const c10::cuda::CUDAGuard guard(src.device());
+        cudaStream_t st = c10::cuda::getCurrentCUDAStream(src.device().index()).stream();
+        check(gsr_multimem_broadcast(reinterpret_cast<void*>(mc_dst_ptr), src.data_ptr<float>(), (size_t)n_floats, (void*)st));
+    }, "store n floats through an NVLS multicast address into every rank's copy (include/gsr.h)");
     m.def("l1_ssim_forward", [](const torch::Tensor& img, const torch::Tensor& gt, double lambda_dssim, bool need_grad) {
         TORCH_CHECK(img.is_cuda() && gt.is_cuda(), "l1_ssim_forward: CUDA tensors only (there is no CPU path)");
         TORCH_CHECK(img.scalar_type() == torch::kFloat32 && gt.scalar_type() == torch::kFloat32, "float32 images");

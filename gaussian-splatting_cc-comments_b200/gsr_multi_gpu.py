@@ -327,7 +327,28 @@ class MultiViewExchange:
         if not self.pack_mc:
             self.pack_handle, self.pack = None, None
         self.small_mode = "multimem" if self.pack_mc else "nccl"
-        if self.mode == "allgather":
+        self.stage_mc = 0
+        if self.mode == "multicast":
+            # the all-gather done by the switch: the staging buffer is a symmetric allocation bound to an NVLS multicast
+            # address; every rank stores its block ONCE through that address (gsr_multimem_broadcast) and the switch
+            # replicates it into all copies.  Falls back to the NCCL all-gather, collectively, where multicast is missing.
+            try:
+                self.block = torch.zeros(n, dtype=torch.float32, device=self.device)
+                self.stage = self._symm.empty(self.world * n, dtype=torch.float32, device=self.device)
+                self.stage.zero_()
+                self.handle = self._symm.rendezvous(self.stage, self.group)
+                self.stage_mc = int(getattr(self.handle, "multicast_ptr", 0) or 0)
+            except Exception as e:
+                self.stage_mc = 0
+                if self.rank == 0:
+                    print("gsr_multi_gpu: multicast staging unavailable (%s); using the NCCL all-gather" % (e,), file=sys.stderr)
+            if not self.stage_mc:
+                self.mode = "allgather"
+            else:
+                self.peer_ptrs = None
+        if self.mode == "multicast":
+            pass
+        elif self.mode == "allgather":
             self.block = torch.zeros(n, dtype=torch.float32, device=self.device)
             self.stage = torch.zeros(self.world * (n + 64 * self.views_per_rank), dtype=torch.float32, device=self.device)
             self.handle, self.peer_ptrs = None, None
@@ -415,6 +436,16 @@ class MultiViewExchange:
                 ptrs = [out[i * nb:].data_ptr() for i in range(self.world * self.views_per_rank)]
                 C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
                 self._mark("sh_kernel_done", self.side)
+            elif self.mode == "multicast":
+                C.multimem_broadcast(self.stage_mc + 4 * self.rank * n, self.block, n)
+                self.handle.barrier(channel=0)    # every rank's stores have left; all copies hold all blocks
+                self.ev_ag.record(self.side)
+                self._mark("allgather_done", self.side)
+                base = self.stage.data_ptr()
+                ptrs = [base + 4 * i * nb for i in range(self.world * self.views_per_rank)]
+                C.multiview_sh_grad(ptrs, means3D, grad_sh, int(sh_degree))
+                self._mark("sh_kernel_done", self.side)
+                self.handle.barrier(channel=1)    # nobody stores the next step's block over one a peer is still reading
             else:
                 self.handle.barrier(channel=0)    # every rank's dL/dRGB and campos are in place
                 self.ev_ag.record(self.side)

@@ -202,6 +202,13 @@ int gsr_unpack_small_grads(int begin, int end, const float* small_pack, float* d
  * after (all slices broadcast).  No reference counterpart (multi-view training extension). */
 int gsr_multimem_allreduce(void* multicast_base, size_t begin, size_t end, int rank, int world, void* cuda_stream);
 
+/* One rank's part of an all-gather done by the NVSwitch: n_floats (a multiple of 4) from local memory are stored once through
+ * the multicast address `multicast_dst` (16-byte aligned; this rank's slot of a buffer every rank allocated symmetrically and
+ * bound to one NVLS multicast object) and land in every rank's copy.  The caller places a device barrier after it on every
+ * rank before reading.  Used for the dL_drgb blocks of multi-view training instead of an NCCL all-gather.  No reference
+ * counterpart. */
+int gsr_multimem_broadcast(void* multicast_dst, const float* src, size_t n_floats, void* cuda_stream);
+
 /* ---- Fused L1 + SSIM training loss (replaces utils/loss_utils.py:17-64 + train.py:126-127) ----
  * Images are `planes` x H x W float32 (planes = channels, or batch*channels: the window is applied per plane and every
  * mean is over all planes*H*W elements, as F.conv2d(groups = channels) + .mean() do).  Window 11, sigma 1.5, zero padding.

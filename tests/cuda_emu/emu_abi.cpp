@@ -22,6 +22,7 @@ GSR_EMU_DEFINE_CUDART
 // csrc/gsr_exchange.cu is NVLS multimem PTX (multi-GPU only): not emulated
 namespace gsr {
 void launch_multimem_allreduce(float*, size_t, size_t, int, int, int, cudaStream_t) { std::abort(); }
+void launch_multimem_broadcast(float*, const float*, size_t, int, cudaStream_t) { std::abort(); }
 }
 
 #include "_gen/gsr_api.cpp"

@@ -208,6 +208,10 @@ def test_exchange_entry_points_check_their_arguments(lib):
     assert lib.gsr_multimem_allreduce(None, 0, 16, 0, 2, None) == 1            # no multicast address
     assert lib.gsr_multimem_allreduce(C.c_void_p(0x1000), 2, 16, 0, 2, None) == 1   # range start not 16-byte aligned
     assert lib.gsr_multimem_allreduce(C.c_void_p(0x1000), 0, 16, 2, 2, None) == 1   # rank outside the world
+    lib.gsr_multimem_broadcast.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    assert lib.gsr_multimem_broadcast(None, None, 0, None) == 0                    # nothing to send
+    assert lib.gsr_multimem_broadcast(C.c_void_p(0x1000), C.c_void_p(0x2000), 6, None) == 1   # not a multiple of 4 floats
+    assert lib.gsr_multimem_broadcast(C.c_void_p(0x1004), C.c_void_p(0x2000), 8, None) == 1   # destination not 16-byte aligned
     lib.gsr_unpack_small_grads.argtypes = [C.c_int, C.c_int] + [C.c_void_p] * 7
     assert lib.gsr_unpack_small_grads(0, 0, None, None, None, None, None, None, None) == 0    # empty range: no-op
     assert lib.gsr_unpack_small_grads(0, 8, None, None, None, None, None, None, None) == 1

@@ -2,6 +2,7 @@
 and end_step() with the fused exchange enabled must equal the sum of all views' single-view gradients, for one and two
 views per rank.  Skipped with fewer than 2 GPUs (bench.py runs the same check before its timed region at N > 1)."""
 import os
+import sys
 import socket
 
 import numpy as np
@@ -34,12 +35,14 @@ def _worker(rank, world, port, q):
         errs = {}
         # bench.exchange_check: every rank computes every view locally (no exchange) -> the expected sum, then runs its own
         # views through the fused exchange twice.  One and two views per rank, both transports, odd P (block alignment).
-        for mode, chunks in (("allgather", 1), ("allgather", 4), ("peer", 1)):     # 4: the pipelined ranges (gsr_multiview_sh_grad_range)
+        for mode, chunks in (("allgather", 1), ("allgather", 4), ("peer", 1), ("multicast", 1)):     # 4: the pipelined ranges (gsr_multiview_sh_grad_range)
             os.environ["GSR_MULTIVIEW_MODE"] = mode
             os.environ["GSR_MV_AG_CHUNKS"] = str(chunks)
             for vpr in (1, 2):
                 r = B.exchange_check(mod, dev, rank, world, vpr, P=40001)
                 errs["%s%d/vpr%d" % (mode, chunks, vpr)] = r["max_rel_l2"]
+                if rank == 0 and r["transport"] != mode:
+                    print("test_multiview_2gpu: mode %s ran as %s on this box" % (mode, r["transport"]), file=sys.stderr)
         q.put((rank, errs))
     finally:
         dist.destroy_process_group()
