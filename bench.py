@@ -685,12 +685,15 @@ def cpu_torch_baseline(budget_s=12.0):
 def roofline_block(stage, P, R, N, P_vis, K, hbm_peak, peak_src, steps):
     """Per-stage algorithmic bytes (restated in DESIGN.md) over the CUDA-event mean of each stage."""
     tiles_bits_passes = 2
+    # <= 8192 tiles: the one-pass counting tile sort (no separate ranges stage): keys read by the count pass, keys + ids
+    # read and ids written by the scatter pass; else two radix passes + a pass over the sorted keys for the ranges
+    counting = not (stage.get("tile_ranges") and stage["tile_ranges"][0] is not None and stage["tile_ranges"][0] >= 0)
     alg = {
         "preprocess": P * (44 + 8) + P_vis * (12 * K + 40),
         "depth_sort": 4 * (8 + 16) * P,                    # 4 LSD passes: histogram read 4 B + scatter read/write 8+8 B per Gaussian... (keys 4 B re-read)
         "scan": 8 * P + 8 * P,                             # gather tiles_touched in depth order + exclusive scan
         "duplicate": 20 * P + 8 * R,                       # 4 B tile key + 4 B id per instance
-        "tile_sort": tiles_bits_passes * (4 + 16) * R,     # 2 passes on 32-bit tile keys: 4 B histogram read + 16 B scatter
+        "tile_sort": (4 + 12) * R if counting else tiles_bits_passes * (4 + 16) * R,   # radix: per pass 4 B histogram read + 16 B scatter
         "tile_ranges": 4 * R,
         "render": 40 * R + 20 * N,
         "bwd_zero": 48 * P,

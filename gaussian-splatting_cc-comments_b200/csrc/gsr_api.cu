@@ -9,6 +9,7 @@
 #include <cstdlib>
 #include <cmath>
 #include "gsr_internal.cuh"
+#include <cstring>
 #include <string>
 #include <cstdio>
 #include <atomic>
@@ -258,9 +259,14 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     if (!bptr) return fail(GSR_ERR_ALLOC, "resize callback returned NULL");
     BinState bin = BinState::carve((char*)align_up((size_t)bptr, 256), R);
 
+    // Instance list -> grouped by tile.  Grids of at most TC_MAX_TILES tiles (1080p: 8160): one counting pass with the tile
+    // cursors in shared memory, which also yields the ranges; larger grids (4K): two LSD radix passes on the tile id and
+    // a pass over the sorted keys for the ranges.  GSR_TILE_SORT=radix forces the second (tests compare the two).
+    const char* forced = getenv("GSR_TILE_SORT");           // read per call: the tests switch it inside one process
+    const bool counting = tile_count_sort_applies(tiles) && !(forced && !strcmp(forced, "radix"));
     const int tile_bits = bits_for((uint32_t)tiles);
     const int npass = (tile_bits + 7) / 8;
-    int s = npass & 1;       // start so that the last pass lands in vals[0] == point_list
+    int s = counting ? 1 : (npass & 1);       // start so that the last pass lands in vals[0] == point_list
     {
         StageTimer t(ST_DUPLICATE, st);
         launch_duplicate(P, geom.vals[0], geom.offsets, geom.tt_sorted, use_rects ? geom.rect_sorted : nullptr, geom.packed, radii, grid_x, grid_y,
@@ -268,7 +274,10 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
                          bin.keys[s], bin.vals[s], st);
     }
     GSR_STAGE("duplicate", st, a->debug);
-    {
+    if (counting) {
+        StageTimer t(ST_TILE_SORT, st);
+        tile_count_sort(bin.keys[1], bin.vals[1], R, tiles, bin.table, bin.vals[0], img.ranges, st);
+    } else {
         StageTimer t(ST_TILE_SORT, st);
         // digits of equal width (13 tile bits -> 7 + 6): fewer bins per pass = longer contiguous runs per block
         const int per = npass ? (tile_bits + npass - 1) / npass : 0;
@@ -283,7 +292,7 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
         for (int pass = 0; pass < npass; pass++) radix_sort_u32(bin.keys, bin.vals, s ^ (pass & 1), R, 1, shifts + pass, bits + pass, bin.table, st);
     }
     GSR_STAGE("tile sort", st, a->debug);
-    { StageTimer t(ST_RANGES, st); launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st); }
+    if (!counting) { StageTimer t(ST_RANGES, st); launch_tile_ranges(R, bin.keys[0], img.ranges, tiles, st); }
     GSR_STAGE("tile ranges", st, a->debug);
     {
         StageTimer t(ST_RENDER, st);

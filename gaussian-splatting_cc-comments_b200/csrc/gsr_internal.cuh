@@ -49,6 +49,23 @@ constexpr int SCAN_TILE = SCAN_THREADS * SCAN_ITEMS;   // 4096
 static inline size_t rs_blocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
 static inline size_t rs_table_words(size_t n) { return 1280 + 4 * rs_blocks(n) * RS_BINS; }   // see radix_sort_u32
 static inline size_t scan_blocks(size_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
+// Counting tile sort (tile_count_sort, gsr_binning.cu): one pass over the instance list with the per-tile write cursors in
+// shared memory, for grids of at most TC_MAX_TILES tiles.  The list is cut into at most TC_MAX_CHUNKS contiguous chunks (one
+// block each, TC_BLOCKS_PER_SM per SM); table = [totals | per-chunk counts, then per-chunk bases].
+constexpr int TC_MAX_TILES = 8192;
+constexpr int TC_THREADS = 256;
+constexpr int TC_EPT = 4;                                // instances per thread and round of the scatter pass
+constexpr int TC_ROUND = TC_THREADS * TC_EPT;
+constexpr int TC_BLOCKS_PER_SM = 3;                      // measured on B200 at R = 12 M: 2-4 chunks per SM 0.153-0.155 ms, 6: 0.169 (table traffic grows)
+constexpr int TC_MAX_CHUNKS = 148 * TC_BLOCKS_PER_SM;
+static inline size_t tc_chunk(size_t R) {
+    size_t c = (R + TC_MAX_CHUNKS - 1) / TC_MAX_CHUNKS;
+    if (c < 4 * (size_t)TC_ROUND) c = 4 * (size_t)TC_ROUND;
+    return (c + TC_ROUND - 1) / TC_ROUND * TC_ROUND;
+}
+static inline size_t tc_chunks(size_t R) { return (R + tc_chunk(R) - 1) / tc_chunk(R); }
+constexpr size_t TC_ROWS_AT = (size_t)TC_MAX_TILES;               // [per-tile totals | one row of counts, then bases, per chunk]
+static inline size_t tc_table_words(size_t R) { return TC_ROWS_AT + tc_chunks(R) * (size_t)TC_MAX_TILES; }
 
 struct GeomState {
     float4* packed;            // 3P float4
@@ -89,7 +106,7 @@ struct GeomState {
 struct BinState {
     uint32_t* vals[2];         // R each; vals[0] is the final point_list
     uint32_t* keys[2];         // R each: tile ids, ping-pong
-    uint32_t* table;           // rs_blocks(R) * RS_BINS + 512
+    uint32_t* table;           // max(rs_table_words(R), tc_table_words(R)): radix look-back tables or the counting sort's chunk counts
     uint32_t* scan_tmp;
     uint8_t* warp_mask;        // R: bit w (0..3) = 8x8 block w of the instance's tile blended it in the forward (backward's cull)
     size_t bytes;
@@ -98,6 +115,7 @@ struct BinState {
         b.vals[0] = c.take<uint32_t>(R); b.vals[1] = c.take<uint32_t>(R);
         b.keys[0] = c.take<uint32_t>(R); b.keys[1] = c.take<uint32_t>(R);
         size_t tbl = rs_table_words(R);
+        if (tc_table_words(R) > tbl) tbl = tc_table_words(R);
         b.table = c.take<uint32_t>(tbl);
         b.scan_tmp = c.take<uint32_t>(scan_blocks(tbl) + 1);
         b.warp_mask = c.take<uint8_t>(R);
@@ -166,6 +184,10 @@ void launch_duplicate(int P, const uint32_t* order, const uint32_t* offsets, con
                       uint32_t* tile_keys, uint32_t* vals, cudaStream_t st);
 
 void launch_tile_ranges(size_t R, const uint32_t* sorted_tile_keys, uint2* ranges, size_t tiles, cudaStream_t st);
+// one-pass counting sort of the instance list by tile + the tile ranges (grids of at most TC_MAX_TILES tiles)
+bool tile_count_sort_applies(size_t tiles);
+void tile_count_sort(const uint32_t* keys, const uint32_t* vals, size_t R, size_t tiles, uint32_t* table, uint32_t* out, uint2* ranges,
+                     cudaStream_t st);
 
 void launch_render_forward(int grid_x, int row_begin, int row_end, const uint2* ranges, const uint32_t* point_list,
                            int W, int H, const float4* packed, const float* bg, float* out_color,

@@ -55,8 +55,23 @@ struct Barrier {                   // reusable barrier over the LIVE threads of 
     }
 };
 
+struct NamedBarrier {              // bar.sync / bar.arrive id, count: completes when `count` threads have arrived or synced
+    std::mutex mu; std::condition_variable cv; int arrived = 0; unsigned long gen = 0;
+    void arrive(int count) {
+        std::unique_lock<std::mutex> lk(mu);
+        if (++arrived == count) { arrived = 0; gen++; cv.notify_all(); }
+    }
+    void sync(int count) {
+        std::unique_lock<std::mutex> lk(mu);
+        const unsigned long g = gen;
+        if (++arrived == count) { arrived = 0; gen++; cv.notify_all(); }
+        else cv.wait(lk, [&] { return gen != g; });
+    }
+};
+
 struct BlockCtx {
     Barrier block;
+    NamedBarrier named[16];
     Barrier warp[32];
     uint32_t xchg[32][32];         // per warp, per lane exchange slots
     std::atomic<int> count{0};     // __syncthreads_count
@@ -83,6 +98,7 @@ extern thread_local dim3 blockDim, gridDim;
 
 // ---- intrinsics used by the kernels under test -----------------------------------------------------------------
 inline void __syncthreads() { emu::g_ctx.block.wait(); }
+inline void __threadfence_block() { std::atomic_thread_fence(std::memory_order_seq_cst); }
 
 inline uint32_t emu_exchange(uint32_t v, int src_lane) {
     emu::BlockCtx& c = emu::g_ctx;

@@ -164,10 +164,13 @@ def test_whole_rasterizer_on_the_host_against_the_reference_builds_b200_fixture(
         assert _rel_l2(g[mine], z[ref]) <= 1e-4, mine          # north_star: gradients 1e-4 relative L2
 
 
-def test_raw_parameter_path_through_the_abi_equals_the_activated_path(abi):
+def test_raw_parameter_path_through_the_abi_equals_the_activated_path(abi, monkeypatch):
     """gsr_forward / gsr_backward with raw_activations + split SH storage: the wiring of include/gsr.h's new fields through
     csrc/gsr_api.cu into the kernels, against the same ABI called with activated / concatenated tensors."""
     import torch
+    # two whole forwards: with the radix tile sort here (the counting sort's warp-to-warp token is an OS-thread wake-up chain
+    # in the emulator; the fixture test above runs it)
+    monkeypatch.setenv("GSR_TILE_SORT", "radix")
     z = np.load(os.path.join(GOLDEN, "ref_cuda_sh3_160x96.npz"))
     P = z["in_means3D"].shape[0]
     rng = np.random.default_rng(0)

@@ -33,6 +33,11 @@ def test_roofline_block_reports_the_dominant_kernel_and_its_committed_ncu_figure
     for name, s in out["stages"].items():
         assert s["alg_bytes"] > 0 and abs(s["gbs"] - s["alg_bytes"] / s["ms"] / 1e6) < 1.0, name
     assert "pair_rate" in out
+    assert out["stages"]["tile_sort"]["alg_bytes"] == 2 * 20 * R             # two radix passes when a ranges stage was timed
+    # the counting tile sort (grids of at most 8192 tiles) has no ranges stage: the library reports it as not sampled
+    stage2 = dict(stage, tile_sort=(0.155, 20), tile_ranges=(-1.0, 0))
+    out2 = b.roofline_block(stage2, P, R, 1920 * 1080, int(0.77 * P), 16, 6551.0, "measured", 20)
+    assert "tile_ranges" not in out2["stages"] and out2["stages"]["tile_sort"]["alg_bytes"] == 16 * R
 
 
 def test_roofline_block_leaves_traffic_null_for_a_workload_without_a_capture():

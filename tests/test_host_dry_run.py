@@ -35,6 +35,9 @@ def test_every_first_gpu_run_test_covered_by_the_dry_run():
 def test_graft_entry_smoke_runs_on_the_host_and_matches_the_oracle():
     """__graft_entry__.smoke() -- the driver's round-end check on cuda:0 -- through the host binding: same Python, same
     binding source, same kernels' logic; sorted lists, ranges, radii, image and gradients against the oracle."""
-    r = subprocess.run([sys.executable, TOOL, "--scripts", "--smoke"], capture_output=True, text=True, timeout=1500)
+    # GSR_TILE_SORT=radix: the counting tile sort hands a token from warp to warp, which is one OS-thread wake-up chain per
+    # turn in the emulator (2 minutes for this scene); tests/test_abi_emulated.py runs it on the reference build's fixtures
+    r = subprocess.run([sys.executable, TOOL, "--scripts", "--smoke"], capture_output=True, text=True, timeout=1500,
+                       env=dict(os.environ, GSR_TILE_SORT="radix"))
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
     assert "smoke ok" in r.stdout and "ok  __graft_entry__.smoke()" in r.stdout

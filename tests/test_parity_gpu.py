@@ -134,6 +134,32 @@ def test_forward_is_deterministic_and_backward_close(mod):
         assert Hh.rel_l2(a["grads"][k], b["grads"][k]) <= 1e-5
 
 
+@pytest.mark.parametrize("W,H,P,s0", [(32, 32, 20000, 6.0), (48, 16, 3000, 40.0), (250, 130, 20000, 3.0), (1920, 1080, 300000, 2.0),
+                                      (1920, 1088, 50000, 30.0)])
+def test_counting_tile_sort_equals_the_radix_tile_sort(mod, W, H, P, s0):
+    """Grids of at most 8192 tiles take the one-pass counting sort (csrc/gsr_binning.cu tile_count_sort), larger ones the two
+    LSD radix passes; GSR_TILE_SORT=radix forces the latter.  Same point list, ranges and image, bit for bit -- from four
+    tiles (every round of the counting pass is contested) to 1080p, and 1920x1088 = 8160 tiles with splats over hundreds of tiles."""
+    cam = S.make_camera(W, H)
+    scene = S.make_scene(P, cam, sh_degree=1, M=4, seed=11, s0_pix=s0)
+    dL = S.upstream_grad(cam)
+    old = os.environ.get("GSR_TILE_SORT")
+    try:
+        os.environ["GSR_TILE_SORT"] = "radix"
+        a = Hh.run_torch(mod, cam, scene, dL)
+        os.environ.pop("GSR_TILE_SORT")
+        b = Hh.run_torch(mod, cam, scene, dL)
+    finally:
+        if old is None:
+            os.environ.pop("GSR_TILE_SORT", None)
+        else:
+            os.environ["GSR_TILE_SORT"] = old
+    assert a["num_rendered"] == b["num_rendered"] and a["num_rendered"] > 0
+    assert (a["point_list"] == b["point_list"]).all()
+    assert (a["ranges"] == b["ranges"]).all()
+    assert (a["color"].view(np.uint32) == b["color"].view(np.uint32)).all()
+
+
 def test_empty_and_invisible_inputs(mod):
     import torch
     cam = S.make_camera(64, 48)

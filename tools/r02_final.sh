@@ -6,7 +6,7 @@ timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4 | tee gpurun_out/
 timeout 600 python bench.py > gpurun_out/r02_final_bench_b200.json 2> gpurun_out/r02_final_bench_b200.err; echo "bench rc=$?"
 timeout 600 python bench.py --impl reference > gpurun_out/r02_final_bench_reference.json 2> gpurun_out/r02_final_bench_reference.err; echo "reference rc=$?"
 timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r02_final_launches.csv python bench.py --steps 3 --warmup 3 --no-cpu-baseline --no-extras > gpurun_out/r02_final_ncu_launches.log 2>&1; echo "ncu list rc=$?"
-timeout 600 ncu --set full --clock-control none --import-source on -k regex:"preprocess_|rs_|scan_|gather_u32|duplicate_|tile_ranges|render_" -s 19 -c 19 -o /tmp/prof_final -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extras > gpurun_out/r02_final_ncu_full.log 2>&1; echo "ncu full rc=$?"
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"preprocess_|rs_|scan_|gather_|duplicate_|tc_|tile_ranges|render_" -s 17 -c 17 -o /tmp/prof_final -f python bench.py --steps 1 --warmup 3 --no-cpu-baseline --no-extras > gpurun_out/r02_final_ncu_full.log 2>&1; echo "ncu full rc=$?"
 ncu -i /tmp/prof_final.ncu-rep --page raw --csv > gpurun_out/r02_final_prof_raw.csv 2>/dev/null
 ncu -i /tmp/prof_final.ncu-rep --page source --csv --kernel-name regex:render_bwd_kernel > gpurun_out/r02_final_src_bwd.csv 2>/dev/null
 ncu -i /tmp/prof_final.ncu-rep --page source --csv --kernel-name regex:render_fwd_kernel > gpurun_out/r02_final_src_fwd.csv 2>/dev/null
