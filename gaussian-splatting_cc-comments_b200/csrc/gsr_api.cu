@@ -259,8 +259,8 @@ int gsr_forward(const gsr_forward_args* a, gsr_resize_fn geom_fn, void* geom_use
     if (!bptr) return fail(GSR_ERR_ALLOC, "resize callback returned NULL");
     BinState bin = BinState::carve((char*)align_up((size_t)bptr, 256), R);
 
-    // Instance list -> grouped by tile.  Grids of at most TC_MAX_TILES tiles (1080p: 8160): one counting pass with the tile
-    // cursors in shared memory, which also yields the ranges; larger grids (4K): two LSD radix passes on the tile id and
+    // Instance list -> grouped by tile.  Grids of at most TC_MAX_TILES tiles (1080p: 8160, 4K: 32 400): one counting pass with
+    // the tile cursors in shared memory, which also yields the ranges; larger grids: LSD radix passes on the tile id and
     // a pass over the sorted keys for the ranges.  GSR_TILE_SORT=radix forces the second (tests compare the two).
     const char* forced = getenv("GSR_TILE_SORT");           // read per call: the tests switch it inside one process
     const bool counting = tile_count_sort_applies(tiles) && !(forced && !strcmp(forced, "radix"));

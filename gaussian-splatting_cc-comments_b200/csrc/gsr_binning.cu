@@ -13,6 +13,7 @@
 // Stability of (2) keeps depth order (and index order among equal depths) inside each tile.
 // All of it is HBM-bound integer work: coalesced key loads, warp-level match_any ranking in
 // shared memory, no tensor cores.
+#include <cstdlib>
 #include "gsr_internal.cuh"
 #include "gsr_smem.cuh"
 #include "gsr_math.cuh"
@@ -341,9 +342,10 @@ void radix_sort_u32(uint32_t* const keys[2], uint32_t* const vals[2], int s0, si
     }
     int s = s0;
     for (int p = 0; p < npass; p++) {
-        // digits of fewer than 8 bits (the two tile-id passes): per-bit ballots beat match.any; measured on B200
+        // one ballot per digit bit beats match.any (one trip per distinct value among the 32 lanes); measured on B200 for the
+        // 6- and 7-bit tile digits (0.30 -> 0.25 ms) and for the 8-bit depth digits (0.1765 -> 0.1667 ms)
         // (tiles of 8 or 12 items per thread measured slower than 16 for both sorts)
-        if (bits[p] < 8)
+        if (bits[p] <= 8)
             rs_sweep_kernel<true, RS_ITEMS><<<nb, RS_THREADS, 0, st>>>(keys[s], vals[s], keys[s ^ 1], vals[s ^ 1], n, shifts[p], bits[p],
                                                                        table + p * RS_BINS, table + 1024 + p, table + 1280 + (size_t)p * nb * RS_BINS);
         else
@@ -421,7 +423,7 @@ __global__ void __launch_bounds__(1024) tc_colscan_kernel(uint32_t* __restrict__
 // cursor updates -- one shared-memory atomic and one read-back per lane and 32 instances, performed in order -- are inside
 // the turn; loads, the rare fix-up and the stores overlap with the other warps' turns and with the other blocks of the SM.
 template <int EPT>
-__global__ void __launch_bounds__(TC_THREADS, TC_BLOCKS_PER_SM) tc_scatter_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
+__global__ void __launch_bounds__(TC_THREADS, 3) tc_scatter_kernel(const uint32_t* __restrict__ keys, const uint32_t* __restrict__ vals,
                                                                               size_t R, size_t chunk, int T, int Tpad, int tile_bits,
                                                                               const uint32_t* __restrict__ table, uint32_t* __restrict__ out, uint2* __restrict__ ranges) {
     GSR_DYN_SMEM(s_dyn);
@@ -527,22 +529,22 @@ void tile_count_sort(const uint32_t* keys, const uint32_t* vals, size_t R, size_
                      cudaStream_t st) {
     const int T = (int)tiles, Tpad = (T + 31) & ~31;
     if (R == 0) { cudaMemsetAsync(ranges, 0, tiles * sizeof(uint2), st); return; }
-    const size_t chunk = tc_chunk(R);
-    const int C = (int)tc_chunks(R);
-    const size_t count_smem = (size_t)Tpad * 4;
-    const size_t scatter_smem = (size_t)Tpad * 4;
-
-    tc_count_kernel<<<C, TC_THREADS, count_smem, st>>>(keys, R, chunk, Tpad, table);
-    tc_colscan_kernel<<<Tpad / 32, 1024, 0, st>>>(table, C, Tpad);
-    int tile_bits = 0;
-    while ((1u << tile_bits) < (unsigned)T) tile_bits++;
-static bool configured[GSR_MAX_DEVICES] = {};
+    const size_t chunk = tc_chunk(R, tiles);
+    const int C = (int)tc_chunks(R, tiles);
+    const size_t smem = (size_t)Tpad * 4;                                  // the chunk's counters / cursors
+    static bool configured[GSR_MAX_DEVICES] = {};
     int dev = 0;
     if (cudaGetDevice(&dev) == cudaSuccess && dev >= 0 && dev < GSR_MAX_DEVICES && !configured[dev]) {
+        cudaFuncSetAttribute(tc_count_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_MAX_TILES * 4);
+        cudaFuncSetAttribute(tc_scatter_kernel<TC_EPT>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_MAX_TILES * 4);
         cudaFuncSetAttribute(tc_scatter_kernel<TC_EPT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         configured[dev] = true;
     }
-    tc_scatter_kernel<TC_EPT><<<C, TC_THREADS, scatter_smem, st>>>(keys, vals, R, chunk, T, Tpad, tile_bits, table, out, ranges);
+    int tile_bits = 0;
+    while ((1u << tile_bits) < (unsigned)T) tile_bits++;
+    tc_count_kernel<<<C, TC_THREADS, smem, st>>>(keys, R, chunk, Tpad, table);
+    tc_colscan_kernel<<<Tpad / 32, 1024, 0, st>>>(table, C, Tpad);
+    tc_scatter_kernel<TC_EPT><<<C, TC_THREADS, smem, st>>>(keys, vals, R, chunk, T, Tpad, tile_bits, table, out, ranges);
     count_launch(3);
 }
 

@@ -50,22 +50,30 @@ static inline size_t rs_blocks(size_t n) { return (n + RS_TILE - 1) / RS_TILE; }
 static inline size_t rs_table_words(size_t n) { return 1280 + 4 * rs_blocks(n) * RS_BINS; }   // see radix_sort_u32
 static inline size_t scan_blocks(size_t n) { return (n + SCAN_TILE - 1) / SCAN_TILE; }
 // Counting tile sort (tile_count_sort, gsr_binning.cu): one pass over the instance list with the per-tile write cursors in
-// shared memory, for grids of at most TC_MAX_TILES tiles.  The list is cut into at most TC_MAX_CHUNKS contiguous chunks (one
-// block each, TC_BLOCKS_PER_SM per SM); table = [totals | per-chunk counts, then per-chunk bases].
-constexpr int TC_MAX_TILES = 8192;
+// shared memory, for grids of at most TC_MAX_TILES tiles.  The list is cut into contiguous chunks (one
+// block each, tc_blocks_per_sm per SM); table = [totals | per-chunk counts, then per-chunk bases].
+constexpr int TC_MAX_TILES = 32768;                      // 128 KB of cursors: 3840x2160 is 32 400 tiles
 constexpr int TC_THREADS = 256;
 constexpr int TC_EPT = 4;                                // instances per thread and round of the scatter pass
 constexpr int TC_ROUND = TC_THREADS * TC_EPT;
-constexpr int TC_BLOCKS_PER_SM = 3;                      // measured on B200 at R = 12 M: 2-4 chunks per SM 0.153-0.155 ms, 6: 0.169 (table traffic grows)
-constexpr int TC_MAX_CHUNKS = 148 * TC_BLOCKS_PER_SM;
-static inline size_t tc_chunk(size_t R) {
-    size_t c = (R + TC_MAX_CHUNKS - 1) / TC_MAX_CHUNKS;
+// chunks (blocks) per SM: what the cursors leave room for.  Measured on B200 at R = 12 M, 8160 tiles: 2-4 per SM 0.153-0.155 ms,
+// 6: 0.169 ms (count table, column scan and prologue traffic grow with the number of chunks)
+static inline int tc_blocks_per_sm(size_t tiles) { return tiles <= 8192 ? 3 : (tiles <= 16384 ? 2 : 1); }
+static inline size_t tc_chunk(size_t R, size_t tiles) {
+    const size_t max_chunks = 148 * (size_t)tc_blocks_per_sm(tiles);
+    size_t c = (R + max_chunks - 1) / max_chunks;
     if (c < 4 * (size_t)TC_ROUND) c = 4 * (size_t)TC_ROUND;
     return (c + TC_ROUND - 1) / TC_ROUND * TC_ROUND;
 }
-static inline size_t tc_chunks(size_t R) { return (R + tc_chunk(R) - 1) / tc_chunk(R); }
+static inline size_t tc_chunks(size_t R, size_t tiles) { return (R + tc_chunk(R, tiles) - 1) / tc_chunk(R, tiles); }
 constexpr size_t TC_ROWS_AT = (size_t)TC_MAX_TILES;               // [per-tile totals | one row of counts, then bases, per chunk]
-static inline size_t tc_table_words(size_t R) { return TC_ROWS_AT + tc_chunks(R) * (size_t)TC_MAX_TILES; }
+// upper bound over all grids: chunks x padded tiles is at most 444 x 8192, 296 x 16384 or 148 x 32768 words (19 MB)
+static inline size_t tc_table_words(size_t R) {
+    size_t rows = 0;
+    const size_t t[3] = {8192, 16384, 32768};
+    for (int i = 0; i < 3; i++) rows = rows > tc_chunks(R, t[i]) * t[i] ? rows : tc_chunks(R, t[i]) * t[i];
+    return TC_ROWS_AT + rows;
+}
 
 struct GeomState {
     float4* packed;            // 3P float4
