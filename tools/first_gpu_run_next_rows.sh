@@ -6,7 +6,7 @@ set -u
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests -m gpu -q -rxX -k "not zz_next" 2>&1 | tail -5 | tee gpurun_out/r02_pytest_gpu_established.log
 timeout 600 python -m pytest tests/test_zz_next_rows_gpu.py -m gpu -q -rxX 2>&1 | tail -40 | tee gpurun_out/r02_pytest_gpu_next_rows.log
-timeout 120 compute-sanitizer --tool memcheck python -m pytest tests/test_zz_next_rows_gpu.py -m gpu -q -x -k "1000 or 257 or 777 or 129 or fixture" > gpurun_out/r02_memcheck_next_rows.log 2>&1; echo "memcheck rc=$?"; tail -3 gpurun_out/r02_memcheck_next_rows.log
+# (compute-sanitizer is closed on this GPU pool; the memory check of these kernels is tools/emu_sanitize.sh on the host)
 python tests/golden/make_golden_knn_gpu.py > gpurun_out/r02_make_golden_knn.log 2>&1; echo "knn golden rc=$?"
 timeout 420 python tools/bench_next.py all > gpurun_out/r02_bench_next.jsonl 2> gpurun_out/r02_bench_next.err; echo "bench_next rc=$?"; cat gpurun_out/r02_bench_next.jsonl | cut -c1-400
 timeout 300 python tools/train_c3.py --impl b200 > gpurun_out/r02_c3_b200.json 2> gpurun_out/r02_c3_b200.err; echo "c3 b200 rc=$?"
