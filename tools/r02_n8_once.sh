@@ -2,7 +2,7 @@ set -u
 mkdir -p gpurun_out
 TAG=${1:-n8}
 shift || true
-env "$@" GSR_MV_TIMELINE=1 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus 8 --steps 20 --warmup 5 --no-extras > gpurun_out/r02_n8_$TAG.json 2> gpurun_out/r02_n8_$TAG.err
+env "$@" GSR_MV_TIMELINE=1 timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 bench.py --gpus 8 --steps 20 --warmup 5 > gpurun_out/r02_n8_$TAG.json 2> gpurun_out/r02_n8_$TAG.err
 python - <<PY
 import json
 j = json.loads(open("gpurun_out/r02_n8_$TAG.json").read().strip().splitlines()[-1])
