@@ -379,7 +379,8 @@ __global__ void __launch_bounds__(TC_THREADS) tc_count_kernel(const uint32_t* __
     // chunk is a multiple of TC_ROUND and the key array is 16-byte aligned: whole 16-byte words up to the last few keys
     const size_t n4 = (e - b) >> 2;
     const uint4* k4 = reinterpret_cast<const uint4*>(keys + b);
-    for (size_t i = threadIdx.x; i < n4; i += TC_THREADS) {
+#pragma unroll 4
+    for (size_t i = threadIdx.x; i < n4; i += TC_THREADS) {               // unrolled: several 16-byte loads in flight per thread
         const uint4 q = __ldg(k4 + i);
         atomicAdd(&s_cnt[q.x], 1u); atomicAdd(&s_cnt[q.y], 1u); atomicAdd(&s_cnt[q.z], 1u); atomicAdd(&s_cnt[q.w], 1u);
     }
@@ -560,7 +561,9 @@ void launch_gather_u32(const uint32_t* src, const uint32_t* idx, uint32_t* dst, 
     count_launch(1);
 }
 
-// tiles_touched and the tile rectangle into depth order in one pass (the rectangle only for Gaussians that emit instances)
+// tiles_touched and the tile rectangle into depth order in one pass (the rectangle only for Gaussians that emit instances).
+// One Gaussian per thread: four per thread (more gathers in flight per thread) measured slower, 0.057 against 0.051 ms for the
+// stage at P = 3 M -- the strided 8-byte stores of the rectangles cost more than the extra loads in flight gain.
 __global__ void __launch_bounds__(256) gather_tt_rect_kernel(const uint32_t* __restrict__ tt, const uint2* __restrict__ rects,
                                                              const uint32_t* __restrict__ idx, uint32_t* __restrict__ tt_sorted,
                                                              uint2* __restrict__ rect_sorted, size_t n) {
