@@ -135,7 +135,7 @@ def test_forward_is_deterministic_and_backward_close(mod):
 
 
 @pytest.mark.parametrize("W,H,P,s0", [(32, 32, 20000, 6.0), (48, 16, 3000, 40.0), (250, 130, 20000, 3.0), (1920, 1080, 300000, 2.0),
-                                      (1920, 1088, 50000, 30.0), (3840, 2160, 200000, 4.0)])
+                                      (1920, 1088, 50000, 30.0), (2560, 1440, 100000, 3.0), (3840, 2160, 200000, 4.0)])
 def test_counting_tile_sort_equals_the_radix_tile_sort(mod, W, H, P, s0):
     """Grids of at most 8192 tiles take the one-pass counting sort (csrc/gsr_binning.cu tile_count_sort), larger ones the two
     LSD radix passes; GSR_TILE_SORT=radix forces the latter.  Same point list, ranges and image, bit for bit -- from four
