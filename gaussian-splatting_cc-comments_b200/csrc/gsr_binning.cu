@@ -523,7 +523,12 @@ __global__ void __launch_bounds__(TC_THREADS, 3) tc_scatter_kernel(const uint32_
     }
 }
 
-bool tile_count_sort_applies(size_t tiles) { return tiles >= 1 && tiles <= (size_t)TC_MAX_TILES; }
+bool tile_count_sort_applies(size_t tiles) {
+#ifdef GSR_EMU
+    if (tiles * 4 > 96 * 1024) return false;          // the host emulation's dynamic shared memory window (tests/cuda_emu/emu.h)
+#endif
+    return tiles >= 1 && tiles <= (size_t)TC_MAX_TILES;
+}
 
 // (tile key, id) in list order -> ids grouped by tile in `out`, tile ranges in `ranges`.  `table`: tc_table_words(R) words.
 void tile_count_sort(const uint32_t* keys, const uint32_t* vals, size_t R, size_t tiles, uint32_t* table, uint32_t* out, uint2* ranges,
