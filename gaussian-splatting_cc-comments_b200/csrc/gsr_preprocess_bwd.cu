@@ -394,6 +394,10 @@ __global__ void __launch_bounds__(256) preprocess_bwd_kernel_generic(PreprocessB
 // culled Gaussians and for coefficients beyond the active degree).  The 27 other floats per Gaussian are
 // staged the same way, so every global store instruction of a warp covers one contiguous 512-byte span.
 constexpr int PB = 128;
+// Resident blocks per SM the staged kernels are compiled for.  6 -> 80 registers, no spills; at 8 (64 registers) ptxas spills
+// ~100 bytes per thread and the kernel waits on its own spill stores: measured 0.319 ms at 8, 0.318 at 7, 0.284 at 6, 0.293 at
+// 5, 0.322 at 4, 0.381 at 10 (C2, P = 3 M).
+constexpr int PB_MINB = 6;
 // floats of output staging per block; the last 14 per Gaussian are the packed small-gradient rows (multi-view exchange)
 constexpr int PB_OUT = 44 * PB;     // mean2D 3 | conic 4 | opacity 1 | colour 3 | mean3D 3 | cov3D 6 | scale 3 | rot 4 | masked rgb 3
 
@@ -522,8 +526,8 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
         const int S4 = (L + 3) / 4, Ss = 4 * (S4 % 2 == 1 ? S4 : S4 + 1);        // odd number of 16-byte words per row
         size_t dyns = (size_t)PB_OUT * sizeof(float);
         if ((size_t)PB * Ss * sizeof(float) > dyns) dyns = (size_t)PB * Ss * sizeof(float);
-        if (a.raw_act) preprocess_bwd_kernel_staged<8, false, true, true><<<(a.P + PB - 1) / PB, PB, dyns, st>>>(a, Ss);
-        else preprocess_bwd_kernel_staged<8, false, false, true><<<(a.P + PB - 1) / PB, PB, dyns, st>>>(a, Ss);
+        if (a.raw_act) preprocess_bwd_kernel_staged<PB_MINB, false, true, true><<<(a.P + PB - 1) / PB, PB, dyns, st>>>(a, Ss);
+        else preprocess_bwd_kernel_staged<PB_MINB, false, false, true><<<(a.P + PB - 1) / PB, PB, dyns, st>>>(a, Ss);
         count_launch(1);
         return;
     }
@@ -536,9 +540,9 @@ void launch_preprocess_backward(const PreprocessBwdArgs& a, cudaStream_t st) {
         ac.begin = bounds[c]; ac.P = bounds[c + 1];
         const int n = ac.P - ac.begin;
         if (n <= 0) continue;
-        if (staged && a.small_pack) preprocess_bwd_kernel_staged<8, true, false, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
-        else if (staged && a.raw_act) preprocess_bwd_kernel_staged<8, false, true, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
-        else if (staged) preprocess_bwd_kernel_staged<8, false, false, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        if (staged && a.small_pack) preprocess_bwd_kernel_staged<PB_MINB, true, false, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        else if (staged && a.raw_act) preprocess_bwd_kernel_staged<PB_MINB, false, true, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
+        else if (staged) preprocess_bwd_kernel_staged<PB_MINB, false, false, false><<<(n + PB - 1) / PB, PB, dyn, st>>>(ac, S);
         else if (a.raw_act) preprocess_bwd_kernel_generic<true><<<(n + 255) / 256, 256, 0, st>>>(ac);
         else preprocess_bwd_kernel_generic<false><<<(n + 255) / 256, 256, 0, st>>>(ac);
         count_launch(1);

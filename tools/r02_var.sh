@@ -7,6 +7,6 @@ while [ $# -ge 2 ]; do
   python - <<PY
 import json
 j = json.loads(open("gpurun_out/r02_var_$TAG.json").read().strip().splitlines()[-1])
-print("$TAG: ms/step %.4f" % j["ms_per_step"], {k: v["ms"] for k, v in j["stages"].items() if k in ("depth_sort", "tile_sort", "scan", "duplicate")})
+print("$TAG: ms/step %.4f" % j["ms_per_step"], {k: v["ms"] for k, v in j["stages"].items() if k in ("depth_sort", "tile_sort", "preprocess", "preprocess_bwd")})
 PY
 done
