@@ -525,7 +525,7 @@ __global__ void __launch_bounds__(TC_THREADS, 3) tc_scatter_kernel(const uint32_
 
 bool tile_count_sort_applies(size_t tiles) {
 #ifdef GSR_EMU
-    if (tiles * 4 > 96 * 1024) return false;          // the host emulation's dynamic shared memory window (tests/cuda_emu/emu.h)
+    if (tiles * 4 > 96 * 1024) return false;          // host builds of this file (GSR_EMU) have a 96 KiB dynamic shared-memory window
 #endif
     return tiles >= 1 && tiles <= (size_t)TC_MAX_TILES;
 }
